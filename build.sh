@@ -1,0 +1,54 @@
+#!/usr/bin/env bash
+# Builds sponge_b200/lib/libposeidon_b200.so (sm_100a) and the CPU oracle oracle/liboracle.so.
+# Usage: ./build.sh [--fast]    (--fast: only the BN254/BLS t=3 and t=5 kernels, for development)
+set -euo pipefail
+cd "$(dirname "$0")"
+SRC=sponge_b200/csrc
+OBJ=build/obj
+LIB=sponge_b200/lib
+mkdir -p "$OBJ" "$LIB"
+NVCC=${NVCC:-nvcc}
+NVFLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
+TS="2 3 4 5 6 7 8 9"
+if [[ "${1:-}" == "--fast" ]]; then TS="3 5"; fi
+
+pids=()
+run() { "$@" & pids+=($!); }
+newer() { # newer <target> <deps...>: true if target missing or older than any dep
+  local t=$1; shift
+  [[ ! -f $t ]] && return 0
+  for d in "$@"; do [[ $d -nt $t ]] && return 0; done
+  return 1
+}
+HDRS=$(ls $SRC/*.cuh $SRC/*.hpp include/*.h)
+for f in 0 1; do
+  for t in $TS; do
+    o=$OBJ/tu_${f}_${t}.o
+    if newer $o $SRC/tu_sponge.cu $HDRS; then
+      run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_TU_T=$t -c -o $o $SRC/tu_sponge.cu
+    fi
+  done
+done
+for u in misc_kernels api; do
+  o=$OBJ/$u.o
+  if newer $o $SRC/$u.cu $HDRS; then run $NVCC $NVFLAGS -c -o $o $SRC/$u.cu; fi
+done
+for u in params opt_constants; do
+  o=$OBJ/$u.o
+  if newer $o $SRC/$u.cpp $HDRS; then run g++ -O2 -std=c++17 -fPIC -c -o $o $SRC/$u.cpp; fi
+done
+fail=0
+for p in "${pids[@]:-}"; do [[ -n "$p" ]] && { wait "$p" || fail=1; }; done
+[[ $fail -eq 0 ]] || { echo "build failed" >&2; exit 1; }
+OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/params.o $OBJ/opt_constants.o"
+for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o"; done; done
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $LIB/libposeidon_b200.so $OBJS -Xcompiler -fPIC
+# CPU oracle (test infrastructure)
+if newer oracle/liboracle.so oracle/poseidon_oracle.c; then
+  gcc -O3 -fopenmp -shared -fPIC -o oracle/liboracle.so oracle/poseidon_oracle.c
+fi
+# host emulation of the device arithmetic (test infrastructure)
+if newer tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $HDRS; then
+  g++ -O2 -std=c++17 -shared -fPIC -o tests/emu/libfp_emu.so tests/emu/fp_emu.cpp
+fi
+echo "built $LIB/libposeidon_b200.so"

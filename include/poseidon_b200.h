@@ -1,0 +1,219 @@
+/* poseidon_b200.h -- C ABI of the B200-native batched Poseidon sponge engine.
+ *
+ * This is the drop-in boundary for ONE path of arkworks-rs/sponge: the Poseidon permutation and
+ * the duplex absorb/squeeze bookkeeping of `PoseidonSponge<F>` (reference: src/poseidon/mod.rs),
+ * lifted to N independent sponges that advance in lock-step on one GPU.  A Rust FFI crate
+ * (`impl CryptographicSponge for B200PoseidonSponge<F>`), the C++ wrapper
+ * include/poseidon_b200.hpp and the Python ctypes binding sponge_b200/ all bind exactly these
+ * symbols.  There is no CPU fallback behind any of them: every call that computes runs the
+ * sm_100a kernels or returns PSD_ERR_CUDA.
+ *
+ * Element format.  One field element is 32 bytes = 4 little-endian u64 limbs, which is the memory
+ * image of `ark_ff::Fp<MontBackend<_,4>,4>` (a Rust `&[Fr]` is an AoS array of these).
+ *   PSD_REPR_MONTGOMERY : the limbs hold x*2^256 mod p  (what `Fr.0.0` holds; zero-cost for Rust)
+ *   PSD_REPR_CANONICAL  : the limbs hold x              (`into_bigint()`); inputs must be < p
+ * Layout of a batch of n sponges with w elements each:
+ *   PSD_LAYOUT_AOS : elem(i,k) at u64 offset (i*w + k)*4                       (Rust slice order)
+ *   PSD_LAYOUT_SOA : elem(i,k) is split in two 16-byte halves h=0,1 stored at
+ *                    u64 offset ((k*2 + h)*n + i)*2  -- a warp reads 32 consecutive 16-byte words
+ * State lanes follow the reference: capacity lanes first, rate lanes at [capacity + j]
+ * (mod.rs:128,143,159).
+ *
+ * Memory spaces.  PSD_MEM_DEVICE: pointers are device pointers on the context's device and the
+ * call is asynchronous on `stream`.  PSD_MEM_HOST: pointers are host memory (pinned or pageable);
+ * the library stages through device buffers it owns, overlapping H2D, kernel and D2H, and returns
+ * when the outputs are in host memory.
+ *
+ * Threading: a psd_ctx is immutable after creation and may be shared between threads; batch calls
+ * with PSD_MEM_HOST serialise on the context's staging buffers.  psd_batch / psd_sponge handles
+ * are not thread-safe (same as `&mut self` in the reference).
+ *
+ * Errors: every function returns a psd_status; nothing aborts or throws across the ABI
+ * (the reference panics: shape asserts mod.rs:196-203, unwrap absorb.rs:163).
+ */
+#ifndef POSEIDON_B200_H
+#define POSEIDON_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum psd_status {
+    PSD_OK = 0,
+    PSD_ERR_ARG = 1,          /* null pointer, unknown enum value, n too large */
+    PSD_ERR_SHAPE = 2,        /* PoseidonConfig::new shape asserts (mod.rs:196-203) would fire */
+    PSD_ERR_NONCANONICAL = 3, /* a canonical input is >= p (ark-ff from_bigint -> None) */
+    PSD_ERR_CUDA = 4,         /* CUDA runtime error; see psd_last_error_string */
+    PSD_ERR_UNSUPPORTED = 5,  /* e.g. state width outside [2,9], rate < 2 for Merkle */
+    PSD_ERR_NOMEM = 6         /* host/device allocation failed, or constant bank full */
+} psd_status;
+
+typedef enum psd_field { PSD_FIELD_BN254_FR = 0, PSD_FIELD_BLS12_381_FR = 1 } psd_field;
+typedef enum psd_repr { PSD_REPR_CANONICAL = 0, PSD_REPR_MONTGOMERY = 1 } psd_repr;
+typedef enum psd_layout { PSD_LAYOUT_AOS = 0, PSD_LAYOUT_SOA = 1 } psd_layout;
+typedef enum psd_mem { PSD_MEM_HOST = 0, PSD_MEM_DEVICE = 1 } psd_mem;
+/* DuplexSpongeMode, reference src/lib.rs:198-210 */
+typedef enum psd_mode { PSD_MODE_ABSORBING = 0, PSD_MODE_SQUEEZING = 1 } psd_mode;
+
+/* Mirrors `PoseidonConfig<F>` field for field (reference src/poseidon/mod.rs:23-42; the 0.3.0
+ * release called it PoseidonParameters).  ark is indexed [round][lane], mds [row][col]; each entry
+ * is 4 u64 limbs in `repr`. */
+typedef struct psd_params {
+    int32_t field;            /* psd_field */
+    uint32_t full_rounds;
+    uint32_t partial_rounds;
+    uint64_t alpha;
+    uint32_t rate;
+    uint32_t capacity;
+    const uint64_t* ark;      /* (full_rounds+partial_rounds) * (rate+capacity) * 4 u64 */
+    const uint64_t* mds;      /* (rate+capacity)^2 * 4 u64 */
+    int32_t repr;             /* psd_repr of ark/mds */
+} psd_params;
+
+typedef struct psd_ctx psd_ctx;       /* parameters resident on one GPU */
+typedef struct psd_batch psd_batch;   /* n sponges in lock-step, states resident in HBM */
+typedef struct psd_sponge psd_sponge; /* one PoseidonSponge<F> (a batch of 1) */
+
+/* ---- library ---------------------------------------------------------------------------------- */
+const char* psd_version(void);
+/* Thread-local text of the last error raised on the calling thread. */
+const char* psd_last_error_string(void);
+const char* psd_status_string(psd_status s);
+/* Number of visible CUDA devices (0 if the runtime cannot be initialised). */
+int psd_device_count(void);
+
+/* ---- parameters -------------------------------------------------------------------------------
+ * psd_ctx_create replaces PoseidonConfig::new + the per-sponge `parameters.clone()` of
+ * PoseidonSponge::new (mod.rs:187-213, 226): shapes are validated once, constants are converted to
+ * Montgomery form and uploaded to the device's constant bank once. */
+psd_status psd_ctx_create(const psd_params* params, int device, psd_ctx** out);
+void psd_ctx_destroy(psd_ctx* ctx);
+/* Read back scalar fields of the context's parameter set (ark/mds pointers are NULL). */
+psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out);
+
+/* Host-only parameter generation, replaces find_poseidon_ark_and_mds (traits.rs:105-146) with the
+ * Grain LFSR of grain_lfsr.rs:15-189.  Writes canonical values: ark (full+partial)*(rate+1)*4 u64,
+ * mds (rate+1)^2*4 u64.  prime_bits must equal the field's modulus size (254 / 255). */
+psd_status psd_find_poseidon_ark_and_mds(int32_t field, uint64_t prime_bits, uint32_t rate,
+                                         uint32_t full_rounds, uint32_t partial_rounds,
+                                         uint32_t skip_matrices, uint64_t* ark, uint64_t* mds);
+/* Replaces PoseidonDefaultConfigField::get_default_poseidon_parameters (traits.rs:59-102) for the
+ * default tables of the reference's BLS12-381 Fr (test.rs:13-32); for BN254 Fr the same table
+ * shape is offered with the round numbers of BASELINE.json (rate 2: 8/57, rate 4: 8/60, alpha 5).
+ * Fills the scalar fields of *out and writes ark/mds (canonical) into caller buffers sized for
+ * the worst case: ark 73*9*4 u64, mds 81*4 u64.  Returns PSD_ERR_UNSUPPORTED where the reference
+ * returns None. */
+psd_status psd_default_params(int32_t field, uint32_t rate, int optimized_for_weights,
+                              psd_params* out, uint64_t* ark_buf, uint64_t* mds_buf);
+
+/* ---- representation / layout helpers (ark-ff into_bigint / from_bigint; absorb.rs:106-120) ----
+ * In place over n elements, on the context's device. */
+psd_status psd_to_montgomery(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void* stream);
+psd_status psd_from_montgomery(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void* stream);
+
+/* ---- batch entry points (new) --------------------------------------------------
+ * psd_permute_batch: n independent applications of PoseidonSponge::permute (mod.rs:95-118), in
+ * place; each state is rate+capacity elements. */
+psd_status psd_permute_batch(psd_ctx* ctx, uint64_t* states, size_t n, int layout, int repr, int mem,
+                             void* stream);
+
+/* For each of n sponges: PoseidonSponge::new; absorb(&inputs[i][0..n_absorb]);
+ * squeeze_native_field_elements(n_squeeze)  (mod.rs:219-254, 320-342).  inputs: n*n_absorb
+ * elements, outputs: n*n_squeeze elements, both in `layout`/`repr`. */
+psd_status psd_absorb_squeeze_batch(psd_ctx* ctx, const uint64_t* inputs, size_t n, uint32_t n_absorb,
+                                    uint32_t n_squeeze, uint64_t* outputs, int layout, int repr,
+                                    int mem, void* stream);
+
+/* Same, ending in squeeze_bytes(n_bytes) (mod.rs:256-270): outputs is n*n_bytes bytes, sponge i at
+ * byte offset i*n_bytes. */
+psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, size_t n,
+                                          uint32_t n_absorb, uint32_t n_bytes, uint8_t* outputs,
+                                          int layout, int repr, int mem, void* stream);
+
+/* Merkle root over n_leaves (a power of two) with the 2-to-1 compression
+ *   H(l, r) := { s = PoseidonSponge::new; s.absorb(&[l, r]); s.squeeze_native_field_elements(1)[0] }
+ * (rate >= 2).  leaves: n_leaves elements (AoS); root: 1 element.  Intermediate levels live in a
+ * device scratch buffer the call allocates and frees (n_leaves/2 + n_leaves/4 elements). */
+psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root,
+                           int repr, int mem, void* stream);
+/* One tree level only: out[i] = H(in[2i], in[2i+1]), i < n_pairs (device or host pointers). */
+psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, uint64_t* out, int repr,
+                              int mem, void* stream);
+
+/* ---- lock-step batch of sponges (absorb/squeeze bookkeeping lifted to batch) --------------------
+ * A psd_batch is n PoseidonSponge<F> values that always receive calls of identical shape, so they
+ * share one DuplexSpongeMode; states stay in HBM between calls (SoA, Montgomery). */
+psd_status psd_batch_new(psd_ctx* ctx, size_t n, psd_batch** out);      /* PoseidonSponge::new x n */
+psd_status psd_batch_clone(const psd_batch* b, psd_batch** out);        /* Clone (mod.rs:44) */
+void psd_batch_free(psd_batch* b);
+/* absorb(&[F; k]) on every sponge (mod.rs:232-254). elems: n*k elements. k == 0 is a no-op. */
+psd_status psd_batch_absorb(psd_batch* b, const uint64_t* elems, uint32_t k, int layout, int repr,
+                            int mem);
+/* squeeze_native_field_elements(k) on every sponge (mod.rs:320-342). out: n*k elements. */
+psd_status psd_batch_squeeze_native(psd_batch* b, uint32_t k, uint64_t* out, int layout, int repr,
+                                    int mem);
+/* squeeze_bytes(n_bytes) on every sponge (mod.rs:256-270). out: n*n_bytes bytes. */
+psd_status psd_batch_squeeze_bytes(psd_batch* b, uint32_t n_bytes, uint8_t* out, int mem);
+/* SpongeExt::into_state / from_state (lib.rs:188-195, mod.rs:344-367): states are n*(rate+capacity)
+ * elements; mode/index are shared by the batch. */
+psd_status psd_batch_get_state(const psd_batch* b, uint64_t* states, int layout, int repr, int mem,
+                               int* mode, uint32_t* index);
+psd_status psd_batch_set_state(psd_batch* b, const uint64_t* states, int layout, int repr, int mem,
+                               int mode, uint32_t index);
+size_t psd_batch_size(const psd_batch* b);
+
+/* ---- single-sponge drop-in (CryptographicSponge, lib.rs:105-158; FieldBasedCryptographicSponge,
+ * lib.rs:162-183).  A batch of one: latency-bound, exists for API parity. Host pointers. ---------- */
+psd_status psd_sponge_new(psd_ctx* ctx, psd_sponge** out);                      /* new, mod.rs:219-230 */
+psd_status psd_sponge_clone(const psd_sponge* s, psd_sponge** out);             /* Clone */
+void psd_sponge_free(psd_sponge* s);
+psd_status psd_sponge_absorb(psd_sponge* s, const uint64_t* elems, size_t n, int repr);   /* mod.rs:232-254 */
+/* absorb(&[u8]) -- u64-LE length prefix, 31-byte LE chunks (absorb.rs:122-140) */
+psd_status psd_sponge_absorb_bytes(psd_sponge* s, const uint8_t* bytes, size_t n);
+psd_status psd_sponge_squeeze_native(psd_sponge* s, size_t n, uint64_t* out, int repr);   /* mod.rs:320-342 */
+psd_status psd_sponge_squeeze_bytes(psd_sponge* s, size_t n_bytes, uint8_t* out);         /* mod.rs:256-270 */
+/* squeeze_bits (mod.rs:272-286): one byte (0/1) per bit */
+psd_status psd_sponge_squeeze_bits(psd_sponge* s, size_t n_bits, uint8_t* out);
+/* squeeze_field_elements::<F2> for a non-native target field (mod.rs:288-317, lib.rs:61-100):
+ * out = n elements of `target_field`, canonical. Same field -> native squeeze. */
+psd_status psd_sponge_squeeze_field_elements(psd_sponge* s, int32_t target_field, size_t n, uint64_t* out);
+/* fork(domain), lib.rs:149-157 */
+psd_status psd_sponge_fork(const psd_sponge* s, const uint8_t* domain, size_t n, psd_sponge** out);
+/* SpongeExt, lib.rs:188-195 */
+psd_status psd_sponge_get_state(const psd_sponge* s, uint64_t* state, int repr, int* mode, uint32_t* index);
+psd_status psd_sponge_set_state(psd_sponge* s, const uint64_t* state, int repr, int mode, uint32_t index);
+
+/* ---- host/device memory helpers for callers without a CUDA runtime binding --------------------- */
+psd_status psd_host_alloc(size_t bytes, void** out);   /* pinned host memory */
+void psd_host_free(void* p);
+psd_status psd_device_alloc(psd_ctx* ctx, size_t bytes, void** out);
+void psd_device_free(psd_ctx* ctx, void* p);
+psd_status psd_memcpy_h2d(psd_ctx* ctx, void* dst, const void* src, size_t bytes, void* stream);
+psd_status psd_memcpy_d2h(psd_ctx* ctx, void* dst, const void* src, size_t bytes, void* stream);
+psd_status psd_stream_synchronize(psd_ctx* ctx, void* stream);
+
+/* Synthetic workload generator: element k of stream `seed` = four splitmix64 words
+ * -> 256-bit LE, masked to the modulus size, redrawn until < p; written in `repr` (AoS) to a
+ * device buffer.  Used by bench.py so inputs are identical on host and device. */
+psd_status psd_synth_fill(psd_ctx* ctx, uint64_t* dev_elems, size_t n, uint64_t seed, uint64_t first_index,
+                          int repr, void* stream);
+
+/* ---- measurement hooks -------------------------------------------------------------------------- */
+/* Number of kernels this library has launched in the calling process (monotonic). */
+uint64_t psd_kernel_launch_count(void);
+/* K0: sustained integer-multiply throughput of the device the context lives on.  Runs a
+ * dependent-free IMAD.WIDE.U32 (kind 0), IMAD lo (kind 1) or the library's own mont_mul (kind 2)
+ * loop on every SM and returns multiply (or modmul) results per second. */
+psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* elapsed_ms);
+/* Select the permutation kernel variant for subsequent calls on this context:
+ * 0 = dense (ark -> S-box -> dense MDS every round, the reference's operation order),
+ * 1 = optimised (default; same results). */
+psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POSEIDON_B200_H */

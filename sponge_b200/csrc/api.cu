@@ -1,0 +1,1285 @@
+// C ABI of the B200 Poseidon sponge engine (include/poseidon_b200.h): contexts, the constant-bank
+// slot allocator, host<->device staging pipeline, lock-step batches and the single-sponge drop-in.
+// Host code only; every computation is a launch of the kernels registered by tu_sponge.cu /
+// misc_kernels.cu.  There is deliberately no CPU implementation of the permutation in here.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/poseidon_b200.h"
+#include "kernels.cuh"
+#include "opt_constants.hpp"
+#include "params.hpp"
+#include "registry.hpp"
+
+namespace psd {
+
+// ------------------------------------------------------------------------------------------------
+// Errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string t_last_error;
+
+static psd_status fail(psd_status s, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    t_last_error = buf;
+    return s;
+}
+
+#define PSD_CUDA(call)                                                                              \
+    do {                                                                                            \
+        cudaError_t e__ = (cudaError_t)(call);                                                      \
+        if (e__ != cudaSuccess)                                                                     \
+            return fail(PSD_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                                  \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// Registries filled by static initialisers of the kernel translation units
+// ------------------------------------------------------------------------------------------------
+static std::vector<PoolUploadFn>& pool_uploaders() {
+    static std::vector<PoolUploadFn> v;
+    return v;
+}
+static std::vector<SpongeKernelEntry>& sponge_kernels() {
+    static std::vector<SpongeKernelEntry> v;
+    return v;
+}
+void register_pool_uploader(PoolUploadFn fn) { pool_uploaders().push_back(fn); }
+void register_sponge_kernel(const SpongeKernelEntry& e) { sponge_kernels().push_back(e); }
+
+static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, int variant) {
+    const SpongeKernelEntry* best = nullptr;
+    int best_score = -1;
+    for (const auto& e : sponge_kernels()) {
+        if (e.field != field || e.t != t) continue;
+        if (e.alpha != 0 && e.alpha != alpha) continue;
+        if (e.variant > variant) continue;
+        const int score = (e.alpha == alpha ? 2 : 0) + e.variant * 4;
+        if (score > best_score) {
+            best_score = score;
+            best = &e;
+        }
+    }
+    return best;
+}
+
+static std::atomic<uint64_t> g_launches{0};
+
+// ------------------------------------------------------------------------------------------------
+// Constant-bank slots: the 62 KiB pool is shared by the live contexts of a device.
+// ------------------------------------------------------------------------------------------------
+struct PoolSlot {
+    uint32_t off, len;
+};
+struct DevicePool {
+    std::mutex mu;
+    std::vector<PoolSlot> used;   // sorted by off
+};
+static DevicePool g_pools[64];
+
+static bool pool_alloc(int device, uint32_t len, uint32_t* off) {
+    DevicePool& p = g_pools[device];
+    std::lock_guard<std::mutex> lk(p.mu);
+    uint32_t cur = 0;
+    size_t pos = 0;
+    for (; pos < p.used.size(); pos++) {
+        if (p.used[pos].off - cur >= len) break;
+        cur = p.used[pos].off + p.used[pos].len;
+    }
+    if (cur + len > kConstPoolWords) return false;
+    p.used.insert(p.used.begin() + pos, PoolSlot{cur, len});
+    *off = cur;
+    return true;
+}
+static void pool_free(int device, uint32_t off) {
+    DevicePool& p = g_pools[device];
+    std::lock_guard<std::mutex> lk(p.mu);
+    for (size_t i = 0; i < p.used.size(); i++) {
+        if (p.used[i].off == off) {
+            p.used.erase(p.used.begin() + i);
+            return;
+        }
+    }
+}
+
+}  // namespace psd
+
+using namespace psd;
+
+// ------------------------------------------------------------------------------------------------
+// Context
+// ------------------------------------------------------------------------------------------------
+static const int kStageSlots = 3;
+
+struct psd_ctx {
+    int device = 0;
+    int field = 0;
+    const HostField* hf = nullptr;
+    uint32_t full_rounds = 0, partial_rounds = 0, rate = 0, capacity = 0, t = 0;
+    uint64_t alpha = 0;
+    std::vector<Fe> ark_mont, mds_mont;   // Montgomery copies of the parameters
+    PermDesc desc{};
+    uint32_t pool_off = 0, pool_len = 0;
+    bool pool_held = false;
+    int variant = 1;
+    int sm_count = 0;
+    // staging for PSD_MEM_HOST calls
+    std::mutex stage_mu;
+    cudaStream_t streams[kStageSlots] = {nullptr, nullptr, nullptr};
+    void* stage_in[kStageSlots] = {nullptr, nullptr, nullptr};
+    void* stage_out[kStageSlots] = {nullptr, nullptr, nullptr};
+    size_t stage_in_bytes = 0, stage_out_bytes = 0;
+    int32_t* d_err = nullptr;
+    int32_t* h_err = nullptr;   // pinned
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            prev = -1;
+        }
+        ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+inline const uint32_t* as_u32(const uint64_t* p) { return reinterpret_cast<const uint32_t*>(p); }
+inline uint32_t* as_u32(uint64_t* p) { return reinterpret_cast<uint32_t*>(p); }
+
+bool valid_enum(int v, int max) { return v >= 0 && v <= max; }
+
+// The host-side mirror of the in-kernel sequencer: only the bookkeeping, no field arithmetic
+// (reference src/poseidon/mod.rs:121-182, 232-254, 320-342).
+void advance_mode(uint32_t rate, uint32_t n_absorb, bool do_squeeze, uint32_t n_squeeze, int* mode,
+                  uint32_t* index) {
+    int m = *mode;
+    uint32_t idx = *index;
+    if (n_absorb) {
+        if (m == kModeAbsorbing) {
+            if (idx == rate) idx = 0;
+        } else {
+            idx = 0;
+        }
+        m = kModeAbsorbing;
+        uint32_t rem = n_absorb;
+        while (idx + rem > rate) {
+            rem -= rate - idx;
+            idx = 0;
+        }
+        idx += rem;
+    }
+    if (do_squeeze) {
+        if (m == kModeAbsorbing || idx == rate) idx = 0;
+        m = kModeSqueezing;
+        uint32_t rem = n_squeeze;
+        while (idx + rem > rate) {
+            rem -= rate - idx;
+            idx = 0;
+        }
+        idx += rem;
+    }
+    *mode = m;
+    *index = idx;
+}
+
+LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n) {
+    LaunchCfg cfg;
+    cfg.block = 128;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k->fn, cfg.block, 0) != cudaSuccess ||
+        per_sm < 1)
+        per_sm = 1;
+    const uint64_t full = (uint64_t)ctx->sm_count * per_sm;
+    const uint64_t need = (n + cfg.block - 1) / cfg.block;
+    cfg.grid = (int)std::max<uint64_t>(1, std::min(full, need));
+    return cfg;
+}
+
+LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
+    LaunchCfg cfg;
+    cfg.block = 256;
+    const uint64_t full = (uint64_t)ctx->sm_count * 8;
+    const uint64_t need = (n + cfg.block - 1) / cfg.block;
+    cfg.grid = (int)std::max<uint64_t>(1, std::min(full, need));
+    return cfg;
+}
+
+psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
+    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, ctx->variant);
+    if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
+    if (a.n == 0) return PSD_OK;
+    LaunchCfg cfg = sponge_cfg(ctx, k, a.n);
+    k->fn<<<cfg.grid, cfg.block, 0, stream>>>(a);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    PSD_CUDA(cudaGetLastError());
+    return PSD_OK;
+}
+
+SpongeArgs base_args(const psd_ctx* ctx, uint64_t n) {
+    SpongeArgs a;
+    memset(&a, 0, sizeof a);
+    a.d = ctx->desc;
+    a.n = n;
+    a.err = ctx->d_err;
+    a.mode = kModeAbsorbing;
+    return a;
+}
+
+// Reads and clears the non-canonical-input flag once `stream` is idle.
+psd_status check_err_flag(psd_ctx* ctx, cudaStream_t stream) {
+    PSD_CUDA(cudaMemcpyAsync(ctx->h_err, ctx->d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+    PSD_CUDA(cudaStreamSynchronize(stream));
+    if (*ctx->h_err) {
+        PSD_CUDA(cudaMemsetAsync(ctx->d_err, 0, sizeof(int32_t), stream));
+        PSD_CUDA(cudaStreamSynchronize(stream));
+        return fail(PSD_ERR_NONCANONICAL, "a canonical input element was >= p");
+    }
+    return PSD_OK;
+}
+
+psd_status ensure_staging(psd_ctx* ctx, size_t in_bytes, size_t out_bytes) {
+    if (in_bytes > ctx->stage_in_bytes) {
+        for (int s = 0; s < kStageSlots; s++) {
+            if (ctx->stage_in[s]) cudaFree(ctx->stage_in[s]);
+            ctx->stage_in[s] = nullptr;
+        }
+        ctx->stage_in_bytes = 0;
+        for (int s = 0; s < kStageSlots; s++) PSD_CUDA(cudaMalloc(&ctx->stage_in[s], in_bytes));
+        ctx->stage_in_bytes = in_bytes;
+    }
+    if (out_bytes > ctx->stage_out_bytes) {
+        for (int s = 0; s < kStageSlots; s++) {
+            if (ctx->stage_out[s]) cudaFree(ctx->stage_out[s]);
+            ctx->stage_out[s] = nullptr;
+        }
+        ctx->stage_out_bytes = 0;
+        for (int s = 0; s < kStageSlots; s++) PSD_CUDA(cudaMalloc(&ctx->stage_out[s], out_bytes));
+        ctx->stage_out_bytes = out_bytes;
+    }
+    return PSD_OK;
+}
+
+// Copies rows [first, first+cnt) of a batch of n sponges with w elements each between host and a
+// compact device buffer holding cnt sponges in the same layout.
+psd_status copy_chunk(void* dst, const void* src, int layout, uint64_t n, uint64_t first, uint64_t cnt,
+                      uint32_t w, bool to_device, cudaStream_t stream) {
+    if (cnt == 0 || w == 0) return PSD_OK;
+    const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    if (layout == kLayoutAos) {
+        const size_t bytes = (size_t)cnt * w * 32;
+        if (to_device)
+            PSD_CUDA(cudaMemcpyAsync(dst, (const char*)src + (size_t)first * w * 32, bytes, kind, stream));
+        else
+            PSD_CUDA(cudaMemcpyAsync((char*)dst + (size_t)first * w * 32, src, bytes, kind, stream));
+    } else {
+        // 2*w rows of 16-byte words: host pitch n*16, device pitch cnt*16
+        if (to_device)
+            PSD_CUDA(cudaMemcpy2DAsync(dst, (size_t)cnt * 16, (const char*)src + (size_t)first * 16, (size_t)n * 16,
+                                       (size_t)cnt * 16, (size_t)w * 2, kind, stream));
+        else
+            PSD_CUDA(cudaMemcpy2DAsync((char*)dst + (size_t)first * 16, (size_t)n * 16, src, (size_t)cnt * 16,
+                                       (size_t)cnt * 16, (size_t)w * 2, kind, stream));
+    }
+    return PSD_OK;
+}
+
+// Shape of one staged (PSD_MEM_HOST) batch call.
+struct StagedCall {
+    uint64_t n;
+    const void* h_in;
+    uint32_t in_w;          // elements per sponge copied in
+    void* h_out;
+    uint32_t out_w;         // elements per sponge copied out (0 when out_bytes_per != 0)
+    uint32_t out_bytes_per; // bytes per sponge copied out (squeeze_bytes)
+    int layout;
+    bool in_place;          // output overwrites the input staging buffer (permute_batch)
+};
+
+// H2D -> kernel -> D2H over kStageSlots streams; `fill` completes the SpongeArgs for a chunk.
+template <class Fill>
+psd_status run_staged(psd_ctx* ctx, const StagedCall& c, Fill fill) {
+    if (c.n == 0) return PSD_OK;
+    std::lock_guard<std::mutex> lk(ctx->stage_mu);
+    const size_t in_per = (size_t)c.in_w * 32;
+    const size_t out_per = c.out_bytes_per ? c.out_bytes_per : (size_t)c.out_w * 32;
+    // chunk: at least enough sponges to fill the GPU a few times over, at most ~256 MiB per slot
+    const size_t per = std::max<size_t>(1, in_per + (c.in_place ? 0 : out_per));
+    uint64_t chunk = std::max<uint64_t>((256ull << 20) / per, 1ull << 16);
+    chunk = std::min<uint64_t>(chunk, 1ull << 20);
+    chunk = std::min<uint64_t>(chunk, c.n);
+    psd_status st = ensure_staging(ctx, std::max<size_t>(chunk * in_per, 16), c.in_place ? 0 : std::max<size_t>(chunk * out_per, 16));
+    if (st != PSD_OK) return st;
+    int slot = 0;
+    for (uint64_t first = 0; first < c.n; first += chunk, slot = (slot + 1) % kStageSlots) {
+        const uint64_t cnt = std::min<uint64_t>(chunk, c.n - first);
+        cudaStream_t s = ctx->streams[slot];
+        void* d_in = ctx->stage_in[slot];
+        void* d_out = c.in_place ? d_in : ctx->stage_out[slot];
+        st = copy_chunk(d_in, c.h_in, c.layout, c.n, first, cnt, c.in_w, true, s);
+        if (st != PSD_OK) return st;
+        SpongeArgs a = base_args(ctx, cnt);
+        fill(a, d_in, d_out);
+        st = launch(ctx, a, s);
+        if (st != PSD_OK) return st;
+        if (c.out_bytes_per) {
+            PSD_CUDA(cudaMemcpyAsync((char*)c.h_out + (size_t)first * c.out_bytes_per, d_out,
+                                     (size_t)cnt * c.out_bytes_per, cudaMemcpyDeviceToHost, s));
+        } else {
+            st = copy_chunk(c.h_out, d_out, c.layout, c.n, first, cnt, c.out_w, false, s);
+            if (st != PSD_OK) return st;
+        }
+    }
+    for (int s = 0; s < kStageSlots; s++) PSD_CUDA(cudaStreamSynchronize(ctx->streams[s]));
+    return check_err_flag(ctx, ctx->streams[0]);
+}
+
+psd_status check_batch_args(const psd_ctx* ctx, const void* p, int layout, int repr, int mem) {
+    if (!ctx) return fail(PSD_ERR_ARG, "null context");
+    if (!p) return fail(PSD_ERR_ARG, "null buffer");
+    if (!valid_enum(layout, 1) || !valid_enum(repr, 1) || !valid_enum(mem, 1))
+        return fail(PSD_ERR_ARG, "bad layout/repr/mem value");
+    return PSD_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// Library
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* psd_version(void) { return "poseidon_b200 0.1.0 (sm_100a)"; }
+const char* psd_last_error_string(void) { return t_last_error.c_str(); }
+const char* psd_status_string(psd_status s) {
+    switch (s) {
+        case PSD_OK: return "PSD_OK";
+        case PSD_ERR_ARG: return "PSD_ERR_ARG";
+        case PSD_ERR_SHAPE: return "PSD_ERR_SHAPE";
+        case PSD_ERR_NONCANONICAL: return "PSD_ERR_NONCANONICAL";
+        case PSD_ERR_CUDA: return "PSD_ERR_CUDA";
+        case PSD_ERR_UNSUPPORTED: return "PSD_ERR_UNSUPPORTED";
+        case PSD_ERR_NOMEM: return "PSD_ERR_NOMEM";
+    }
+    return "PSD_ERR_?";
+}
+int psd_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+uint64_t psd_kernel_launch_count(void) { return g_launches.load(); }
+
+// ------------------------------------------------------------------------------------------------
+// Parameters
+// ------------------------------------------------------------------------------------------------
+psd_status psd_find_poseidon_ark_and_mds(int32_t field, uint64_t prime_bits, uint32_t rate, uint32_t full_rounds,
+                                         uint32_t partial_rounds, uint32_t skip_matrices, uint64_t* ark,
+                                         uint64_t* mds) {
+    const HostField* hf = host_field(field);
+    if (!hf) return fail(PSD_ERR_ARG, "unknown field %d", field);
+    if (!ark || !mds) return fail(PSD_ERR_ARG, "null output");
+    if (rate < 1 || rate > 64 || full_rounds + partial_rounds > 4096) return fail(PSD_ERR_ARG, "bad sizes");
+    int rc = find_poseidon_ark_and_mds(*hf, prime_bits, rate, full_rounds, partial_rounds, skip_matrices,
+                                       reinterpret_cast<Fe*>(ark), reinterpret_cast<Fe*>(mds));
+    if (rc == -1) return fail(PSD_ERR_SHAPE, "prime_bits %llu != modulus size %d", (unsigned long long)prime_bits, hf->bits);
+    if (rc != 0) return fail(PSD_ERR_ARG, "x_i + y_j = 0: not a Cauchy matrix");
+    return PSD_OK;
+}
+
+psd_status psd_default_params(int32_t field, uint32_t rate, int optimized_for_weights, psd_params* out,
+                              uint64_t* ark_buf, uint64_t* mds_buf) {
+    const HostField* hf = host_field(field);
+    if (!hf) return fail(PSD_ERR_ARG, "unknown field %d", field);
+    if (!out || !ark_buf || !mds_buf) return fail(PSD_ERR_ARG, "null output");
+    DefaultEntry e;
+    if (!default_entry(field, rate, optimized_for_weights != 0, &e))
+        return fail(PSD_ERR_UNSUPPORTED, "no default parameters for field %d rate %u", field, rate);
+    psd_status st = psd_find_poseidon_ark_and_mds(field, (uint64_t)hf->bits, rate, e.full_rounds, e.partial_rounds,
+                                                  e.skip_matrices, ark_buf, mds_buf);
+    if (st != PSD_OK) return st;
+    out->field = field;
+    out->full_rounds = e.full_rounds;
+    out->partial_rounds = e.partial_rounds;
+    out->alpha = e.alpha;
+    out->rate = rate;
+    out->capacity = 1;   // traits.rs:96
+    out->ark = ark_buf;
+    out->mds = mds_buf;
+    out->repr = PSD_REPR_CANONICAL;
+    return PSD_OK;
+}
+
+psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
+    if (!p || !out) return fail(PSD_ERR_ARG, "null argument");
+    *out = nullptr;
+    const HostField* hf = host_field(p->field);
+    if (!hf) return fail(PSD_ERR_ARG, "unknown field %d", p->field);
+    if (!valid_enum(p->repr, 1)) return fail(PSD_ERR_ARG, "bad repr");
+    if (!p->ark || !p->mds) return fail(PSD_ERR_SHAPE, "ark/mds missing");
+    const uint64_t t64 = (uint64_t)p->rate + p->capacity;
+    const uint64_t rounds64 = (uint64_t)p->full_rounds + p->partial_rounds;
+    if (p->rate == 0) return fail(PSD_ERR_SHAPE, "rate must be >= 1");
+    if (t64 < 2 || t64 > 9) return fail(PSD_ERR_UNSUPPORTED, "state width %llu outside [2,9]", (unsigned long long)t64);
+    if (rounds64 == 0 || rounds64 > 1024) return fail(PSD_ERR_UNSUPPORTED, "round count %llu outside [1,1024]", (unsigned long long)rounds64);
+    const uint32_t t = (uint32_t)t64, rounds = (uint32_t)rounds64;
+    int ndev = psd_device_count();
+    if (device < 0 || device >= ndev || device >= 64)
+        return fail(PSD_ERR_CUDA, "CUDA device %d not available (%d visible); this library has no CPU path", device, ndev);
+
+    psd_ctx* ctx = new (std::nothrow) psd_ctx();
+    if (!ctx) return fail(PSD_ERR_NOMEM, "out of host memory");
+    ctx->device = device;
+    ctx->field = p->field;
+    ctx->hf = hf;
+    ctx->full_rounds = p->full_rounds;
+    ctx->partial_rounds = p->partial_rounds;
+    ctx->rate = p->rate;
+    ctx->capacity = p->capacity;
+    ctx->t = t;
+    ctx->alpha = p->alpha;
+
+    // constants -> Montgomery
+    const Fe* ark = reinterpret_cast<const Fe*>(p->ark);
+    const Fe* mds = reinterpret_cast<const Fe*>(p->mds);
+    ctx->ark_mont.resize((size_t)rounds * t);
+    ctx->mds_mont.resize((size_t)t * t);
+    for (size_t i = 0; i < ctx->ark_mont.size() + ctx->mds_mont.size(); i++) {
+        const bool is_ark = i < ctx->ark_mont.size();
+        const Fe& v = is_ark ? ark[i] : mds[i - ctx->ark_mont.size()];
+        if (hf_cmp(v.v, hf->p) >= 0) {
+            delete ctx;
+            return fail(PSD_ERR_NONCANONICAL, "%s[%zu] >= p", is_ark ? "ark" : "mds", is_ark ? i : i - (size_t)rounds * t);
+        }
+        Fe m = p->repr == PSD_REPR_CANONICAL ? hf_to_mont(*hf, v) : v;
+        if (is_ark) ctx->ark_mont[i] = m;
+        else ctx->mds_mont[i - ctx->ark_mont.size()] = m;
+    }
+
+    // constant-bank image: [ark][mds][one][r2][optimised constants]
+    std::vector<uint32_t> img;
+    auto push_fe = [&img](const Fe& f) {
+        for (int k = 0; k < 4; k++) {
+            img.push_back((uint32_t)f.v[k]);
+            img.push_back((uint32_t)(f.v[k] >> 32));
+        }
+    };
+    PermDesc& d = ctx->desc;
+    d.ark_off = (uint32_t)img.size();
+    for (const Fe& f : ctx->ark_mont) push_fe(f);
+    d.mds_off = (uint32_t)img.size();
+    for (const Fe& f : ctx->mds_mont) push_fe(f);
+    d.one_off = (uint32_t)img.size();
+    push_fe(hf_one(*hf));
+    d.r2_off = (uint32_t)img.size();
+    Fe r2;
+    memcpy(r2.v, hf->r2, 32);
+    push_fe(r2);
+    d.half_full = p->full_rounds / 2;
+    d.partial = p->partial_rounds;
+    d.total = rounds;
+    d.rate = p->rate;
+    d.capacity = p->capacity;
+    d.alpha_lo = (uint32_t)p->alpha;
+    d.alpha_hi = (uint32_t)(p->alpha >> 32);
+    append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
+
+    DeviceGuard guard(device);
+    if (!guard.ok) {
+        delete ctx;
+        return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    }
+    ctx->pool_len = (uint32_t)img.size();
+    if (!pool_alloc(device, ctx->pool_len, &ctx->pool_off)) {
+        delete ctx;
+        return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts", (unsigned)img.size());
+    }
+    ctx->pool_held = true;
+    offset_desc(ctx->desc, ctx->pool_off);
+
+    auto cleanup = [&](psd_status s) {
+        psd_ctx_destroy(ctx);
+        return s;
+    };
+#define CTX_CUDA(call)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t e__ = (cudaError_t)(call);                                                               \
+        if (e__ != cudaSuccess)                                                                              \
+            return cleanup(fail(PSD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)));             \
+    } while (0)
+    cudaDeviceProp prop;
+    CTX_CUDA(cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    for (int s = 0; s < kStageSlots; s++) CTX_CUDA(cudaStreamCreateWithFlags(&ctx->streams[s], cudaStreamNonBlocking));
+    CTX_CUDA(cudaMalloc(&ctx->d_err, sizeof(int32_t)));
+    CTX_CUDA(cudaMemset(ctx->d_err, 0, sizeof(int32_t)));
+    CTX_CUDA(cudaHostAlloc(&ctx->h_err, sizeof(int32_t), cudaHostAllocDefault));
+    *ctx->h_err = 0;
+    for (PoolUploadFn up : pool_uploaders()) CTX_CUDA(up(ctx->pool_off, img.data(), (uint32_t)img.size(), nullptr));
+    CTX_CUDA(cudaDeviceSynchronize());
+#undef CTX_CUDA
+    if (!find_kernel(ctx->field, (int)t, ctx->alpha, ctx->variant))
+        return cleanup(fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u in this build", ctx->field, t));
+    *out = ctx;
+    return PSD_OK;
+}
+
+void psd_ctx_destroy(psd_ctx* ctx) {
+    if (!ctx) return;
+    {
+        DeviceGuard guard(ctx->device);
+        for (int s = 0; s < kStageSlots; s++) {
+            if (ctx->streams[s]) {
+                cudaStreamSynchronize(ctx->streams[s]);
+                cudaStreamDestroy(ctx->streams[s]);
+            }
+            if (ctx->stage_in[s]) cudaFree(ctx->stage_in[s]);
+            if (ctx->stage_out[s]) cudaFree(ctx->stage_out[s]);
+        }
+        if (ctx->d_err) cudaFree(ctx->d_err);
+        if (ctx->h_err) cudaFreeHost(ctx->h_err);
+    }
+    if (ctx->pool_held) pool_free(ctx->device, ctx->pool_off);
+    delete ctx;
+}
+
+psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
+    if (!ctx || !out) return fail(PSD_ERR_ARG, "null argument");
+    out->field = ctx->field;
+    out->full_rounds = ctx->full_rounds;
+    out->partial_rounds = ctx->partial_rounds;
+    out->alpha = ctx->alpha;
+    out->rate = ctx->rate;
+    out->capacity = ctx->capacity;
+    out->ark = nullptr;
+    out->mds = nullptr;
+    out->repr = PSD_REPR_MONTGOMERY;
+    return PSD_OK;
+}
+
+psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
+    if (!ctx) return fail(PSD_ERR_ARG, "null context");
+    if (variant < 0 || variant > 1) return fail(PSD_ERR_ARG, "variant must be 0 or 1");
+    ctx->variant = variant;
+    return PSD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Memory helpers
+// ------------------------------------------------------------------------------------------------
+psd_status psd_host_alloc(size_t bytes, void** out) {
+    if (!out) return fail(PSD_ERR_ARG, "null output");
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? PSD_ERR_NOMEM : PSD_ERR_CUDA, "cudaHostAlloc(%zu): %s", bytes,
+                    cudaGetErrorString(e));
+    }
+    return PSD_OK;
+}
+void psd_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+psd_status psd_device_alloc(psd_ctx* ctx, size_t bytes, void** out) {
+    if (!ctx || !out) return fail(PSD_ERR_ARG, "null argument");
+    *out = nullptr;
+    DeviceGuard guard(ctx->device);
+    cudaError_t e = cudaMalloc(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? PSD_ERR_NOMEM : PSD_ERR_CUDA, "cudaMalloc(%zu): %s", bytes,
+                    cudaGetErrorString(e));
+    }
+    return PSD_OK;
+}
+void psd_device_free(psd_ctx* ctx, void* p) {
+    if (!ctx || !p) return;
+    DeviceGuard guard(ctx->device);
+    cudaFree(p);
+}
+psd_status psd_memcpy_h2d(psd_ctx* ctx, void* dst, const void* src, size_t bytes, void* stream) {
+    if (!ctx || !dst || !src) return fail(PSD_ERR_ARG, "null argument");
+    DeviceGuard guard(ctx->device);
+    PSD_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return PSD_OK;
+}
+psd_status psd_memcpy_d2h(psd_ctx* ctx, void* dst, const void* src, size_t bytes, void* stream) {
+    if (!ctx || !dst || !src) return fail(PSD_ERR_ARG, "null argument");
+    DeviceGuard guard(ctx->device);
+    PSD_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return PSD_OK;
+}
+psd_status psd_stream_synchronize(psd_ctx* ctx, void* stream) {
+    if (!ctx) return fail(PSD_ERR_ARG, "null context");
+    DeviceGuard guard(ctx->device);
+    PSD_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return check_err_flag(ctx, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Representation change, synthetic inputs, K0
+// ------------------------------------------------------------------------------------------------
+static psd_status convert(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void* stream, int to_m) {
+    if (!ctx || (!elems && n)) return fail(PSD_ERR_ARG, "null argument");
+    if (!valid_enum(mem, 1)) return fail(PSD_ERR_ARG, "bad mem");
+    if (n == 0) return PSD_OK;
+    DeviceGuard guard(ctx->device);
+    if (mem == PSD_MEM_DEVICE) {
+        PSD_CUDA(launch_convert(ctx->field, ctx->desc, as_u32(elems), n, to_m, ctx->d_err, misc_cfg(ctx, n), stream));
+        g_launches++;
+        return PSD_OK;
+    }
+    std::lock_guard<std::mutex> lk(ctx->stage_mu);
+    const uint64_t chunk = std::min<uint64_t>(n, 1ull << 22);
+    psd_status st = ensure_staging(ctx, chunk * 32, 0);
+    if (st != PSD_OK) return st;
+    int slot = 0;
+    for (uint64_t first = 0; first < n; first += chunk, slot = (slot + 1) % kStageSlots) {
+        const uint64_t cnt = std::min<uint64_t>(chunk, n - first);
+        cudaStream_t s = ctx->streams[slot];
+        PSD_CUDA(cudaMemcpyAsync(ctx->stage_in[slot], elems + first * 4, cnt * 32, cudaMemcpyHostToDevice, s));
+        PSD_CUDA(launch_convert(ctx->field, ctx->desc, (uint32_t*)ctx->stage_in[slot], cnt, to_m, ctx->d_err,
+                                misc_cfg(ctx, cnt), s));
+        g_launches++;
+        PSD_CUDA(cudaMemcpyAsync(elems + first * 4, ctx->stage_in[slot], cnt * 32, cudaMemcpyDeviceToHost, s));
+    }
+    for (int s = 0; s < kStageSlots; s++) PSD_CUDA(cudaStreamSynchronize(ctx->streams[s]));
+    return check_err_flag(ctx, ctx->streams[0]);
+}
+psd_status psd_to_montgomery(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void* stream) {
+    return convert(ctx, elems, n, mem, stream, 1);
+}
+psd_status psd_from_montgomery(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void* stream) {
+    return convert(ctx, elems, n, mem, stream, 0);
+}
+
+psd_status psd_synth_fill(psd_ctx* ctx, uint64_t* dev_elems, size_t n, uint64_t seed, uint64_t first_index, int repr,
+                          void* stream) {
+    if (!ctx || (!dev_elems && n)) return fail(PSD_ERR_ARG, "null argument");
+    if (!valid_enum(repr, 1)) return fail(PSD_ERR_ARG, "bad repr");
+    if (n == 0) return PSD_OK;
+    DeviceGuard guard(ctx->device);
+    PSD_CUDA(launch_synth(ctx->field, ctx->desc, as_u32(dev_elems), n, seed, first_index, repr, misc_cfg(ctx, n), stream));
+    g_launches++;
+    return PSD_OK;
+}
+
+psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* elapsed_ms) {
+    if (!ctx || !per_second) return fail(PSD_ERR_ARG, "null argument");
+    if (kind < 0 || kind > 2) return fail(PSD_ERR_ARG, "kind must be 0, 1 or 2");
+    DeviceGuard guard(ctx->device);
+    uint32_t* scratch = nullptr;
+    PSD_CUDA(cudaMalloc(&scratch, 1024 * 4));
+    std::vector<uint32_t> init(1024);
+    for (int i = 0; i < 1024; i++) init[i] = 0x9e3779b9u * (i + 1) + 12345u;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    psd_status result = PSD_OK;
+    float ms = 0;
+    LaunchCfg cfg;
+    cfg.block = kind == 2 ? 128 : 256;
+    cfg.grid = ctx->sm_count * (kind == 2 ? 8 : 8);
+    const uint32_t iters = kind == 2 ? 4096 : 16384;
+    do {
+#define K0_CUDA(call)                                                                           \
+    if ((cudaError_t)(call) != cudaSuccess) {                                                   \
+        result = fail(PSD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(cudaGetLastError())); \
+        break;                                                                                  \
+    }
+        K0_CUDA(cudaMemcpy(scratch, init.data(), 4096, cudaMemcpyHostToDevice));
+        K0_CUDA(cudaEventCreate(&e0));
+        K0_CUDA(cudaEventCreate(&e1));
+        cudaStream_t s = ctx->streams[0];
+        for (int w = 0; w < 2; w++) K0_CUDA(launch_imad_peak(ctx->field, kind, scratch, iters, cfg, s));
+        K0_CUDA(cudaEventRecord(e0, s));
+        const int reps = 5;
+        for (int r = 0; r < reps; r++) K0_CUDA(launch_imad_peak(ctx->field, kind, scratch, iters, cfg, s));
+        K0_CUDA(cudaEventRecord(e1, s));
+        K0_CUDA(cudaEventSynchronize(e1));
+        K0_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        g_launches += 7;
+        const double threads = (double)cfg.grid * cfg.block;
+        const double per_thread = kind == 2 ? 2.0 * iters : 64.0 * iters;
+        *per_second = threads * per_thread * reps / (ms * 1e-3);
+        if (elapsed_ms) *elapsed_ms = ms / reps;
+#undef K0_CUDA
+    } while (0);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(scratch);
+    return result;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Batch entry points
+// ------------------------------------------------------------------------------------------------
+psd_status psd_permute_batch(psd_ctx* ctx, uint64_t* states, size_t n, int layout, int repr, int mem, void* stream) {
+    psd_status st = check_batch_args(ctx, n ? (void*)states : (void*)ctx, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    if (n == 0) return PSD_OK;
+    DeviceGuard guard(ctx->device);
+    auto fill = [&](SpongeArgs& a, void* d_in, void* /*d_out*/) {
+        a.state_in = (const uint32_t*)d_in;
+        a.state_in_layout = layout;
+        a.state_in_repr = repr;
+        a.state_out = (uint32_t*)d_in;
+        a.state_out_layout = layout;
+        a.state_out_repr = repr;
+        a.n_raw = 1;
+    };
+    if (mem == PSD_MEM_DEVICE) {
+        SpongeArgs a = base_args(ctx, n);
+        fill(a, states, states);
+        return launch(ctx, a, (cudaStream_t)stream);
+    }
+    StagedCall c{n, states, ctx->t, states, ctx->t, 0, layout, true};
+    return run_staged(ctx, c, fill);
+}
+
+static psd_status absorb_squeeze(psd_ctx* ctx, const uint64_t* inputs, size_t n, uint32_t n_absorb, uint32_t n_squeeze,
+                                 uint64_t* outputs, uint8_t* out_bytes, uint32_t n_bytes, int layout, int repr, int mem,
+                                 void* stream) {
+    psd_status st = check_batch_args(ctx, (n && n_absorb) ? (const void*)inputs : (const void*)ctx, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    const bool bytes_mode = out_bytes != nullptr || (outputs == nullptr && n_bytes);
+    if (n && ((bytes_mode && n_bytes && !out_bytes) || (!bytes_mode && n_squeeze && !outputs)))
+        return fail(PSD_ERR_ARG, "null output buffer");
+    if (n == 0) return PSD_OK;
+    if (bytes_mode) {
+        const uint32_t usable = (uint32_t)(ctx->hf->bits - 1) / 8;
+        n_squeeze = (n_bytes + usable - 1) / usable;   // mod.rs:259
+    }
+    DeviceGuard guard(ctx->device);
+    auto fill = [&](SpongeArgs& a, void* d_in, void* d_out) {
+        a.in = (const uint32_t*)d_in;
+        a.n_absorb = n_absorb;
+        a.in_layout = layout;
+        a.in_repr = repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = n_squeeze;
+        if (bytes_mode) {
+            a.out_bytes = (uint8_t*)d_out;
+            a.n_bytes = n_bytes;
+        } else {
+            a.out = (uint32_t*)d_out;
+            a.out_layout = layout;
+            a.out_repr = repr;
+        }
+    };
+    if (mem == PSD_MEM_DEVICE) {
+        SpongeArgs a = base_args(ctx, n);
+        fill(a, (void*)inputs, bytes_mode ? (void*)out_bytes : (void*)outputs);
+        return launch(ctx, a, (cudaStream_t)stream);
+    }
+    StagedCall c{n, inputs, n_absorb, bytes_mode ? (void*)out_bytes : (void*)outputs, bytes_mode ? 0 : n_squeeze,
+                 bytes_mode ? n_bytes : 0, layout, false};
+    if (bytes_mode && n_bytes == 0) c.out_bytes_per = 0, c.out_w = 0;
+    return run_staged(ctx, c, fill);
+}
+
+psd_status psd_absorb_squeeze_batch(psd_ctx* ctx, const uint64_t* inputs, size_t n, uint32_t n_absorb, uint32_t n_squeeze,
+                                    uint64_t* outputs, int layout, int repr, int mem, void* stream) {
+    return absorb_squeeze(ctx, inputs, n, n_absorb, n_squeeze, outputs, nullptr, 0, layout, repr, mem, stream);
+}
+
+psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, size_t n, uint32_t n_absorb,
+                                          uint32_t n_bytes, uint8_t* outputs, int layout, int repr, int mem, void* stream) {
+    if (n && n_bytes && !outputs) return fail(PSD_ERR_ARG, "null output buffer");
+    static uint8_t dummy;
+    return absorb_squeeze(ctx, inputs, n, n_absorb, 0, nullptr, outputs ? outputs : &dummy, n_bytes, layout, repr, mem, stream);
+}
+
+psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, uint64_t* out, int repr, int mem,
+                              void* stream) {
+    if (ctx && ctx->rate < 2) return fail(PSD_ERR_UNSUPPORTED, "2-to-1 compression needs rate >= 2");
+    return absorb_squeeze(ctx, in, n_pairs, 2, 1, out, nullptr, 0, PSD_LAYOUT_AOS, repr, mem, stream);
+}
+
+psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root, int repr, int mem,
+                           void* stream) {
+    psd_status st = check_batch_args(ctx, leaves, PSD_LAYOUT_AOS, repr, mem);
+    if (st != PSD_OK) return st;
+    if (!root) return fail(PSD_ERR_ARG, "null root");
+    if (ctx->rate < 2) return fail(PSD_ERR_UNSUPPORTED, "2-to-1 compression needs rate >= 2");
+    if (n_leaves == 0 || (n_leaves & (n_leaves - 1))) return fail(PSD_ERR_ARG, "n_leaves must be a power of two");
+    DeviceGuard guard(ctx->device);
+    cudaStream_t s = mem == PSD_MEM_DEVICE ? (cudaStream_t)stream : ctx->streams[0];
+    if (n_leaves == 1) {
+        const cudaMemcpyKind kind = mem == PSD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToHost;
+        PSD_CUDA(cudaMemcpyAsync(root, leaves, 32, kind, s));
+        PSD_CUDA(cudaStreamSynchronize(s));
+        return PSD_OK;
+    }
+    // scratch: [level 1: n/2][level 2: n/4] elements, ping-pong above that; Montgomery inside
+    const size_t half = n_leaves / 2, quarter = std::max<size_t>(n_leaves / 4, 1);
+    uint32_t* scratch = nullptr;
+    uint32_t* d_leaves = nullptr;
+    PSD_CUDA(cudaMalloc(&scratch, (half + quarter) * 32));
+    psd_status result = PSD_OK;
+    do {
+        const uint32_t* src = as_u32(leaves);
+        if (mem == PSD_MEM_HOST) {
+            if (cudaMalloc(&d_leaves, n_leaves * 32) != cudaSuccess) {
+                result = fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for leaves failed", n_leaves * 32);
+                cudaGetLastError();
+                break;
+            }
+            if (cudaMemcpyAsync(d_leaves, leaves, n_leaves * 32, cudaMemcpyHostToDevice, s) != cudaSuccess) {
+                result = fail(PSD_ERR_CUDA, "leaf upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+                break;
+            }
+            src = d_leaves;
+        }
+        uint32_t* bufs[2] = {scratch, scratch + half * 8};
+        int which = 0;
+        int src_repr = repr;
+        for (size_t pairs = half; pairs >= 1; pairs /= 2) {
+            SpongeArgs a = base_args(ctx, pairs);
+            a.in = src;
+            a.n_absorb = 2;
+            a.in_layout = kLayoutAos;
+            a.in_repr = src_repr;
+            a.do_squeeze = 1;
+            a.n_squeeze = 1;
+            a.out = bufs[which];
+            a.out_layout = kLayoutAos;
+            a.out_repr = pairs == 1 ? repr : kReprMontgomery;
+            result = launch(ctx, a, s);
+            if (result != PSD_OK) break;
+            src = bufs[which];
+            src_repr = kReprMontgomery;
+            which ^= 1;
+            if (pairs == 1) break;
+        }
+        if (result != PSD_OK) break;
+        const cudaMemcpyKind kind = mem == PSD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+        if (cudaMemcpyAsync(root, src, 32, kind, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) {
+            result = fail(PSD_ERR_CUDA, "root download failed: %s", cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+        result = check_err_flag(ctx, s);
+    } while (0);
+    cudaStreamSynchronize(s);
+    cudaFree(scratch);
+    if (d_leaves) cudaFree(d_leaves);
+    return result;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Lock-step batches
+// ------------------------------------------------------------------------------------------------
+struct psd_batch {
+    psd_ctx* ctx = nullptr;
+    size_t n = 0;
+    uint32_t* d_state = nullptr;   // SoA, Montgomery, n * t elements
+    int mode = kModeAbsorbing;
+    uint32_t index = 0;
+    cudaStream_t stream = nullptr;
+    void* d_io = nullptr;          // device staging for host-side inputs/outputs
+    size_t d_io_bytes = 0;
+};
+
+namespace {
+
+psd_status batch_io(psd_batch* b, size_t bytes) {
+    if (bytes <= b->d_io_bytes) return PSD_OK;
+    if (b->d_io) cudaFree(b->d_io);
+    b->d_io = nullptr;
+    b->d_io_bytes = 0;
+    if (cudaMalloc(&b->d_io, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) failed", bytes);
+    }
+    b->d_io_bytes = bytes;
+    return PSD_OK;
+}
+
+void batch_state_args(const psd_batch* b, SpongeArgs& a) {
+    a.state_in = b->d_state;
+    a.state_in_layout = kLayoutSoa;
+    a.state_in_repr = kReprMontgomery;
+    a.state_out = b->d_state;
+    a.state_out_layout = kLayoutSoa;
+    a.state_out_repr = kReprMontgomery;
+    a.mode = b->mode;
+    a.index = b->index;
+}
+
+}  // namespace
+
+extern "C" {
+
+psd_status psd_batch_new(psd_ctx* ctx, size_t n, psd_batch** out) {
+    if (!ctx || !out) return fail(PSD_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (n == 0) return fail(PSD_ERR_ARG, "empty batch");
+    DeviceGuard guard(ctx->device);
+    psd_batch* b = new (std::nothrow) psd_batch();
+    if (!b) return fail(PSD_ERR_NOMEM, "out of host memory");
+    b->ctx = ctx;
+    b->n = n;
+    const size_t bytes = n * ctx->t * 32;
+    if (cudaMalloc(&b->d_state, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        delete b;
+        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for batch state failed", bytes);
+    }
+    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMemsetAsync(b->d_state, 0, bytes, b->stream) != cudaSuccess ||   // vec![F::zero(); t], mod.rs:220
+        cudaStreamSynchronize(b->stream) != cudaSuccess) {
+        psd_status st = fail(PSD_ERR_CUDA, "batch init failed: %s", cudaGetErrorString(cudaGetLastError()));
+        psd_batch_free(b);
+        return st;
+    }
+    *out = b;
+    return PSD_OK;
+}
+
+psd_status psd_batch_clone(const psd_batch* b, psd_batch** out) {
+    if (!b || !out) return fail(PSD_ERR_ARG, "null argument");
+    psd_status st = psd_batch_new(b->ctx, b->n, out);
+    if (st != PSD_OK) return st;
+    DeviceGuard guard(b->ctx->device);
+    psd_batch* c = *out;
+    c->mode = b->mode;
+    c->index = b->index;
+    if (cudaStreamSynchronize(b->stream) != cudaSuccess ||
+        cudaMemcpyAsync(c->d_state, b->d_state, b->n * b->ctx->t * 32, cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+        st = fail(PSD_ERR_CUDA, "batch clone failed: %s", cudaGetErrorString(cudaGetLastError()));
+        psd_batch_free(c);
+        *out = nullptr;
+        return st;
+    }
+    return PSD_OK;
+}
+
+void psd_batch_free(psd_batch* b) {
+    if (!b) return;
+    DeviceGuard guard(b->ctx->device);
+    if (b->stream) {
+        cudaStreamSynchronize(b->stream);
+        cudaStreamDestroy(b->stream);
+    }
+    if (b->d_state) cudaFree(b->d_state);
+    if (b->d_io) cudaFree(b->d_io);
+    delete b;
+}
+
+size_t psd_batch_size(const psd_batch* b) { return b ? b->n : 0; }
+
+psd_status psd_batch_absorb(psd_batch* b, const uint64_t* elems, uint32_t k, int layout, int repr, int mem) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    if (k == 0) return PSD_OK;   // empty input: no-op, mod.rs:234-236
+    psd_status st = check_batch_args(b->ctx, elems, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    psd_ctx* ctx = b->ctx;
+    DeviceGuard guard(ctx->device);
+    const uint32_t* d_in = as_u32(elems);
+    if (mem == PSD_MEM_HOST) {
+        const size_t bytes = b->n * (size_t)k * 32;
+        st = batch_io(b, bytes);
+        if (st != PSD_OK) return st;
+        PSD_CUDA(cudaMemcpyAsync(b->d_io, elems, bytes, cudaMemcpyHostToDevice, b->stream));
+        d_in = (const uint32_t*)b->d_io;
+    }
+    SpongeArgs a = base_args(ctx, b->n);
+    batch_state_args(b, a);
+    a.in = d_in;
+    a.n_absorb = k;
+    a.in_layout = layout;
+    a.in_repr = repr;
+    st = launch(ctx, a, b->stream);
+    if (st != PSD_OK) return st;
+    advance_mode(ctx->rate, k, false, 0, &b->mode, &b->index);
+    PSD_CUDA(cudaStreamSynchronize(b->stream));
+    return repr == PSD_REPR_CANONICAL ? check_err_flag(ctx, b->stream) : PSD_OK;
+}
+
+static psd_status batch_squeeze(psd_batch* b, uint32_t k, uint64_t* out, uint8_t* out_bytes, uint32_t n_bytes, int layout,
+                                int repr, int mem) {
+    psd_ctx* ctx = b->ctx;
+    DeviceGuard guard(ctx->device);
+    const bool bytes_mode = out_bytes != nullptr;
+    const size_t out_size = bytes_mode ? b->n * (size_t)n_bytes : b->n * (size_t)k * 32;
+    void* d_out = bytes_mode ? (void*)out_bytes : (void*)out;
+    if (mem == PSD_MEM_HOST) {
+        psd_status st = batch_io(b, std::max<size_t>(out_size, 16));
+        if (st != PSD_OK) return st;
+        d_out = b->d_io;
+    }
+    SpongeArgs a = base_args(ctx, b->n);
+    batch_state_args(b, a);
+    a.do_squeeze = 1;
+    a.n_squeeze = k;
+    if (bytes_mode) {
+        a.out_bytes = (uint8_t*)d_out;
+        a.n_bytes = n_bytes;
+    } else {
+        a.out = (uint32_t*)d_out;
+        a.out_layout = layout;
+        a.out_repr = repr;
+    }
+    psd_status st = launch(ctx, a, b->stream);
+    if (st != PSD_OK) return st;
+    advance_mode(ctx->rate, 0, true, k, &b->mode, &b->index);
+    if (mem == PSD_MEM_HOST && out_size)
+        PSD_CUDA(cudaMemcpyAsync(bytes_mode ? (void*)out_bytes : (void*)out, d_out, out_size, cudaMemcpyDeviceToHost, b->stream));
+    PSD_CUDA(cudaStreamSynchronize(b->stream));
+    return PSD_OK;
+}
+
+psd_status psd_batch_squeeze_native(psd_batch* b, uint32_t k, uint64_t* out, int layout, int repr, int mem) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    static uint64_t dummy[4];
+    psd_status st = check_batch_args(b->ctx, k ? (void*)out : (void*)dummy, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    return batch_squeeze(b, k, out ? out : dummy, nullptr, 0, layout, repr, k ? mem : PSD_MEM_HOST);
+}
+
+psd_status psd_batch_squeeze_bytes(psd_batch* b, uint32_t n_bytes, uint8_t* out, int mem) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    if (!valid_enum(mem, 1)) return fail(PSD_ERR_ARG, "bad mem");
+    if (n_bytes && !out) return fail(PSD_ERR_ARG, "null output");
+    static uint8_t dummy;
+    const uint32_t usable = (uint32_t)(b->ctx->hf->bits - 1) / 8;
+    const uint32_t k = (n_bytes + usable - 1) / usable;
+    return batch_squeeze(b, k, nullptr, out ? out : &dummy, n_bytes, PSD_LAYOUT_AOS, PSD_REPR_CANONICAL,
+                         n_bytes ? mem : PSD_MEM_HOST);
+}
+
+// SpongeExt::into_state / from_state (lib.rs:188-195): a pure layout/representation change done by
+// the sponge kernel with no absorb, squeeze or permutation in between load and store.
+psd_status psd_batch_get_state(const psd_batch* b, uint64_t* states, int layout, int repr, int mem, int* mode,
+                               uint32_t* index) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    psd_status st = check_batch_args(b->ctx, states, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    psd_ctx* ctx = b->ctx;
+    DeviceGuard guard(ctx->device);
+    psd_batch* bm = const_cast<psd_batch*>(b);
+    const size_t bytes = b->n * ctx->t * 32;
+    uint32_t* d_user = as_u32(states);
+    if (mem == PSD_MEM_HOST) {
+        st = batch_io(bm, bytes);
+        if (st != PSD_OK) return st;
+        d_user = (uint32_t*)bm->d_io;
+    }
+    SpongeArgs a = base_args(ctx, b->n);
+    a.state_in = b->d_state;
+    a.state_in_layout = kLayoutSoa;
+    a.state_in_repr = kReprMontgomery;
+    a.state_out = d_user;
+    a.state_out_layout = layout;
+    a.state_out_repr = repr;
+    st = launch(ctx, a, b->stream);
+    if (st != PSD_OK) return st;
+    if (mem == PSD_MEM_HOST) PSD_CUDA(cudaMemcpyAsync(states, d_user, bytes, cudaMemcpyDeviceToHost, b->stream));
+    PSD_CUDA(cudaStreamSynchronize(b->stream));
+    if (mode) *mode = b->mode;
+    if (index) *index = b->index;
+    return PSD_OK;
+}
+
+psd_status psd_batch_set_state(psd_batch* b, const uint64_t* states, int layout, int repr, int mem, int mode,
+                               uint32_t index) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    psd_status st = check_batch_args(b->ctx, states, layout, repr, mem);
+    if (st != PSD_OK) return st;
+    psd_ctx* ctx = b->ctx;
+    if (!valid_enum(mode, 1) || index > ctx->rate) return fail(PSD_ERR_ARG, "bad mode/index");
+    DeviceGuard guard(ctx->device);
+    const size_t bytes = b->n * ctx->t * 32;
+    const uint32_t* d_user = as_u32(states);
+    if (mem == PSD_MEM_HOST) {
+        st = batch_io(b, bytes);
+        if (st != PSD_OK) return st;
+        PSD_CUDA(cudaMemcpyAsync(b->d_io, states, bytes, cudaMemcpyHostToDevice, b->stream));
+        d_user = (const uint32_t*)b->d_io;
+    }
+    SpongeArgs a = base_args(ctx, b->n);
+    a.state_in = d_user;
+    a.state_in_layout = layout;
+    a.state_in_repr = repr;
+    a.state_out = b->d_state;
+    a.state_out_layout = kLayoutSoa;
+    a.state_out_repr = kReprMontgomery;
+    st = launch(ctx, a, b->stream);
+    if (st != PSD_OK) return st;
+    PSD_CUDA(cudaStreamSynchronize(b->stream));
+    if (repr == PSD_REPR_CANONICAL) {
+        st = check_err_flag(ctx, b->stream);
+        if (st != PSD_OK) return st;
+    }
+    b->mode = mode;
+    b->index = index;
+    return PSD_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Single-sponge drop-in: a batch of one.
+// ------------------------------------------------------------------------------------------------
+struct psd_sponge {
+    psd_batch* b = nullptr;
+};
+
+extern "C" {
+
+psd_status psd_sponge_new(psd_ctx* ctx, psd_sponge** out) {
+    if (!ctx || !out) return fail(PSD_ERR_ARG, "null argument");
+    *out = nullptr;
+    psd_sponge* s = new (std::nothrow) psd_sponge();
+    if (!s) return fail(PSD_ERR_NOMEM, "out of host memory");
+    psd_status st = psd_batch_new(ctx, 1, &s->b);
+    if (st != PSD_OK) {
+        delete s;
+        return st;
+    }
+    *out = s;
+    return PSD_OK;
+}
+
+psd_status psd_sponge_clone(const psd_sponge* s, psd_sponge** out) {
+    if (!s || !out) return fail(PSD_ERR_ARG, "null argument");
+    *out = nullptr;
+    psd_sponge* c = new (std::nothrow) psd_sponge();
+    if (!c) return fail(PSD_ERR_NOMEM, "out of host memory");
+    psd_status st = psd_batch_clone(s->b, &c->b);
+    if (st != PSD_OK) {
+        delete c;
+        return st;
+    }
+    *out = c;
+    return PSD_OK;
+}
+
+void psd_sponge_free(psd_sponge* s) {
+    if (!s) return;
+    psd_batch_free(s->b);
+    delete s;
+}
+
+psd_status psd_sponge_absorb(psd_sponge* s, const uint64_t* elems, size_t n, int repr) {
+    if (!s) return fail(PSD_ERR_ARG, "null sponge");
+    if (n == 0) return PSD_OK;
+    if (n > 0xffffffffull) return fail(PSD_ERR_ARG, "too many elements");
+    return psd_batch_absorb(s->b, elems, (uint32_t)n, PSD_LAYOUT_AOS, repr, PSD_MEM_HOST);
+}
+
+psd_status psd_sponge_absorb_bytes(psd_sponge* s, const uint8_t* bytes, size_t n) {
+    if (!s || (!bytes && n)) return fail(PSD_ERR_ARG, "null argument");
+    // absorb.rs:135-139: (len as u64 LE) || bytes, cut into (MODULUS_BIT_SIZE-1)/8-byte LE chunks
+    const size_t usable = (size_t)(s->b->ctx->hf->bits - 1) / 8;
+    std::vector<uint8_t> buf(8 + n);
+    const uint64_t len = (uint64_t)n;
+    for (int i = 0; i < 8; i++) buf[i] = (uint8_t)(len >> (8 * i));
+    if (n) memcpy(buf.data() + 8, bytes, n);
+    const size_t n_el = (buf.size() + usable - 1) / usable;
+    std::vector<uint64_t> elems(n_el * 4, 0);
+    for (size_t i = 0; i < buf.size(); i++) {
+        const size_t e = i / usable, off = i % usable;
+        elems[e * 4 + off / 8] |= (uint64_t)buf[i] << (8 * (off % 8));
+    }
+    return psd_sponge_absorb(s, elems.data(), n_el, PSD_REPR_CANONICAL);
+}
+
+psd_status psd_sponge_squeeze_native(psd_sponge* s, size_t n, uint64_t* out, int repr) {
+    if (!s) return fail(PSD_ERR_ARG, "null sponge");
+    if (n > 0xffffffffull) return fail(PSD_ERR_ARG, "too many elements");
+    return psd_batch_squeeze_native(s->b, (uint32_t)n, out, PSD_LAYOUT_AOS, repr, PSD_MEM_HOST);
+}
+
+psd_status psd_sponge_squeeze_bytes(psd_sponge* s, size_t n_bytes, uint8_t* out) {
+    if (!s) return fail(PSD_ERR_ARG, "null sponge");
+    if (n_bytes > 0xffffffffull) return fail(PSD_ERR_ARG, "too many bytes");
+    return psd_batch_squeeze_bytes(s->b, (uint32_t)n_bytes, out, PSD_MEM_HOST);
+}
+
+psd_status psd_sponge_squeeze_bits(psd_sponge* s, size_t n_bits, uint8_t* out) {
+    if (!s || (!out && n_bits)) return fail(PSD_ERR_ARG, "null argument");
+    // mod.rs:272-286: MODULUS_BIT_SIZE-1 LE bits of each canonical element
+    const size_t usable = (size_t)s->b->ctx->hf->bits - 1;
+    const size_t n_el = (n_bits + usable - 1) / usable;
+    std::vector<uint64_t> elems(std::max<size_t>(n_el, 1) * 4);
+    psd_status st = psd_sponge_squeeze_native(s, n_el, elems.data(), PSD_REPR_CANONICAL);
+    if (st != PSD_OK) return st;
+    for (size_t i = 0; i < n_bits; i++) {
+        const size_t e = i / usable, bit = i % usable;
+        out[i] = (uint8_t)((elems[e * 4 + bit / 64] >> (bit % 64)) & 1);
+    }
+    return PSD_OK;
+}
+
+psd_status psd_sponge_squeeze_field_elements(psd_sponge* s, int32_t target_field, size_t n, uint64_t* out) {
+    if (!s || (!out && n)) return fail(PSD_ERR_ARG, "null argument");
+    const HostField* f2 = host_field(target_field);
+    if (!f2) return fail(PSD_ERR_ARG, "unknown target field %d", target_field);
+    if (target_field == s->b->ctx->field)   // TypeId equal / same characteristic: native, mod.rs:288-317
+        return psd_sponge_squeeze_native(s, n, out, PSD_REPR_CANONICAL);
+    if (n == 0) return PSD_OK;   // lib.rs:65-67
+    // lib.rs:61-100: (MODULUS_BIT_SIZE_F2 - 1) bits per element, LE-packed, from_le_bytes_mod_order
+    const size_t nb = (size_t)f2->bits - 1;
+    std::vector<uint8_t> bits(nb * n);
+    psd_status st = psd_sponge_squeeze_bits(s, nb * n, bits.data());
+    if (st != PSD_OK) return st;
+    for (size_t k = 0; k < n; k++) {
+        Fe v = hf_zero();
+        for (size_t i = 0; i < nb; i++) v.v[i / 64] |= (uint64_t)bits[k * nb + i] << (i % 64);
+        v = hf_reduce(*f2, v);
+        memcpy(out + 4 * k, v.v, 32);
+    }
+    return PSD_OK;
+}
+
+psd_status psd_sponge_fork(const psd_sponge* s, const uint8_t* domain, size_t n, psd_sponge** out) {
+    if (!s || !out || (!domain && n)) return fail(PSD_ERR_ARG, "null argument");
+    // lib.rs:149-157: clone; absorb(&(len as u64 LE bytes || domain) as Vec<u8>)
+    psd_status st = psd_sponge_clone(s, out);
+    if (st != PSD_OK) return st;
+    std::vector<uint8_t> input(8 + n);
+    const uint64_t len = (uint64_t)n;
+    for (int i = 0; i < 8; i++) input[i] = (uint8_t)(len >> (8 * i));
+    if (n) memcpy(input.data() + 8, domain, n);
+    st = psd_sponge_absorb_bytes(*out, input.data(), input.size());
+    if (st != PSD_OK) {
+        psd_sponge_free(*out);
+        *out = nullptr;
+    }
+    return st;
+}
+
+psd_status psd_sponge_get_state(const psd_sponge* s, uint64_t* state, int repr, int* mode, uint32_t* index) {
+    if (!s) return fail(PSD_ERR_ARG, "null sponge");
+    return psd_batch_get_state(s->b, state, PSD_LAYOUT_AOS, repr, PSD_MEM_HOST, mode, index);
+}
+
+psd_status psd_sponge_set_state(psd_sponge* s, const uint64_t* state, int repr, int mode, uint32_t index) {
+    if (!s) return fail(PSD_ERR_ARG, "null sponge");
+    return psd_batch_set_state(s->b, state, PSD_LAYOUT_AOS, repr, PSD_MEM_HOST, mode, index);
+}
+
+}  // extern "C"

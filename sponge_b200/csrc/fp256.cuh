@@ -1,0 +1,329 @@
+// 256-bit Montgomery arithmetic over BN254 Fr and BLS12-381 Fr in 8 x 32-bit limbs (sm_100a).
+//
+// Replaces, on the device, the `ark_ff::Fp<MontBackend<_,4>,4>` operations that the reference's
+// Poseidon permutation bottoms out in (`add_assign`, `mul`, `pow`; call sites
+// /root/reference/src/poseidon/mod.rs:67,72,78,85,87,88,128,143).  Values are Montgomery
+// residues x*2^256 mod p; with R = 2^256 the 4x64-bit (ark-ff) and 8x32-bit (here) limb views are
+// the same bytes.
+//
+// Multiplication is a CIOS Montgomery product whose 32x32->64 partial products are accumulated in
+// two interleaved 64-bit-aligned accumulators ("lo-aligned" columns 0,2,4,6 and "hi-aligned" columns
+// 1,3,5,7).  Each group of four products is one PTX carry chain (mad.lo.cc / madc.hi.cc), which
+// ptxas fuses into IMAD.WIDE.U32 / IMAD.WIDE.U32.X with the carry in a predicate register: one
+// integer-multiply-pipe instruction per 32x32 product and almost no separate carry arithmetic.
+// Every chain is a single asm statement so the compiler can never separate a carry producer from
+// its consumer.
+//
+// The same header compiles with plain g++ (PSD_HOST_EMU): each chain then runs a C model with an
+// explicit carry, which lets tests/ check the limb plumbing on a machine without a GPU.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define PSD_DEV __device__ __forceinline__
+#else
+#define PSD_DEV static inline
+#ifndef PSD_HOST_EMU
+#define PSD_HOST_EMU 1
+#endif
+#endif
+
+namespace psd {
+
+// ------------------------------------------------------------------------------------------------
+// Field descriptors.  P = modulus limbs (LE), NP0 = -p^-1 mod 2^32.
+// BLS12-381 Fr modulus: /root/reference/src/test.rs:6.  BN254 Fr: not in the reference
+// (BASELINE.json configs 1-3); the standard alt_bn128 scalar field.
+// ------------------------------------------------------------------------------------------------
+struct Bn254Fr {
+    static constexpr int kFieldId = 0;
+    static constexpr int kBits = 254;
+    static constexpr uint32_t P0 = 0xf0000001u, P1 = 0x43e1f593u, P2 = 0x79b97091u, P3 = 0x2833e848u,
+                              P4 = 0x8181585du, P5 = 0xb85045b6u, P6 = 0xe131a029u, P7 = 0x30644e72u;
+    static constexpr uint32_t NP0 = 0xefffffffu;
+};
+struct Bls12381Fr {
+    static constexpr int kFieldId = 1;
+    static constexpr int kBits = 255;
+    static constexpr uint32_t P0 = 0x00000001u, P1 = 0xffffffffu, P2 = 0xfffe5bfeu, P3 = 0x53bda402u,
+                              P4 = 0x09a1d805u, P5 = 0x3339d808u, P6 = 0x299d7d48u, P7 = 0x73eda753u;
+    static constexpr uint32_t NP0 = 0xffffffffu;
+};
+
+// ------------------------------------------------------------------------------------------------
+// Carry-chain primitives.  An accumulator is uint32_t[8] holding four (lo,hi) pairs.
+// ------------------------------------------------------------------------------------------------
+
+// d[2k],d[2k+1] = a_k * b   (four independent 32x32->64 products)
+PSD_DEV void mul4(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
+#if !defined(PSD_HOST_EMU)
+    asm("mul.lo.u32 %0, %8, %12;\n\t"
+        "mul.hi.u32 %1, %8, %12;\n\t"
+        "mul.lo.u32 %2, %9, %12;\n\t"
+        "mul.hi.u32 %3, %9, %12;\n\t"
+        "mul.lo.u32 %4, %10, %12;\n\t"
+        "mul.hi.u32 %5, %10, %12;\n\t"
+        "mul.lo.u32 %6, %11, %12;\n\t"
+        "mul.hi.u32 %7, %11, %12;"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    const uint32_t a[4] = {a0, a1, a2, a3};
+    for (int k = 0; k < 4; k++) {
+        uint64_t w = (uint64_t)a[k] * b;
+        d[2 * k] = (uint32_t)w;
+        d[2 * k + 1] = (uint32_t)(w >> 32);
+    }
+#endif
+}
+
+// d (256-bit, as 4 pairs) += {a0,a1,a2,a3} * b  laid out pairwise; the carry out of the top pair is
+// added to `top`.
+PSD_DEV void mad4(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b,
+                  uint32_t& top) {
+#if !defined(PSD_HOST_EMU)
+    asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+        "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+        "addc.u32 %8, %8, 0;"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7]),
+          "+r"(top)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    const uint32_t a[4] = {a0, a1, a2, a3};
+    uint64_t c = 0;
+    for (int k = 0; k < 4; k++) {
+        unsigned __int128 w = (unsigned __int128)((uint64_t)a[k] * b) +
+                              (((uint64_t)d[2 * k + 1] << 32) | d[2 * k]) + c;
+        d[2 * k] = (uint32_t)w;
+        d[2 * k + 1] = (uint32_t)(w >> 32);
+        c = (uint64_t)(w >> 64);
+    }
+    top += (uint32_t)c;
+#endif
+}
+
+// Same, for chains whose carry out is provably zero (see the bound in mont_mul).
+PSD_DEV void mad4_nc(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
+#if !defined(PSD_HOST_EMU)
+    asm("mad.lo.cc.u32 %0, %8, %12, %0;\n\t"
+        "madc.hi.cc.u32 %1, %8, %12, %1;\n\t"
+        "madc.lo.cc.u32 %2, %9, %12, %2;\n\t"
+        "madc.hi.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.lo.cc.u32 %4, %10, %12, %4;\n\t"
+        "madc.hi.cc.u32 %5, %10, %12, %5;\n\t"
+        "madc.lo.cc.u32 %6, %11, %12, %6;\n\t"
+        "madc.hi.u32 %7, %11, %12, %7;"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    uint32_t top = 0;
+    mad4(d, a0, a1, a2, a3, b, top);
+#endif
+}
+
+// The window slides down by one 32-bit column: `x` (whose x[0] is already zero) becomes the new
+// hi-aligned accumulator and `y0` is column 0 of the new lo-aligned one.
+//   y0 += x[1]                                  (carry feeds the chain below)
+//   x[2k],x[2k+1] = a_k*b + (x[2k+2],x[2k+3])   k = 0..2
+//   x[6],x[7]     = a_3*b + carry
+PSD_DEV void mad4_slide(uint32_t* x, uint32_t& y0, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                        uint32_t b) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %8, %8, %1;\n\t"
+        "madc.lo.cc.u32 %0, %9, %13, %2;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %3;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %4;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %5;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %6;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %7;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, 0;\n\t"
+        "madc.hi.u32 %7, %12, %13, 0;"
+        : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]),
+          "+r"(y0)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    const uint32_t a[4] = {a0, a1, a2, a3};
+    uint64_t s = (uint64_t)y0 + x[1];
+    y0 = (uint32_t)s;
+    uint64_t c = s >> 32;
+    for (int k = 0; k < 4; k++) {
+        uint64_t add = (k < 3) ? ((((uint64_t)x[2 * k + 3]) << 32) | x[2 * k + 2]) : 0;
+        unsigned __int128 w = (unsigned __int128)((uint64_t)a[k] * b) + add + c;
+        x[2 * k] = (uint32_t)w;
+        x[2 * k + 1] = (uint32_t)(w >> 32);
+        c = (uint64_t)(w >> 64);
+    }
+#endif
+}
+
+// r = w + (z >> 32), z[0] == 0: merges the two accumulators after the last row.
+PSD_DEV void merge8(uint32_t* r, const uint32_t* w, const uint32_t* z) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, 0;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]),
+          "r"(z[1]), "r"(z[2]), "r"(z[3]), "r"(z[4]), "r"(z[5]), "r"(z[6]), "r"(z[7]));
+#else
+    uint64_t c = 0;
+    for (int k = 0; k < 8; k++) {
+        uint64_t s = (uint64_t)w[k] + (k < 7 ? z[k + 1] : 0) + c;
+        r[k] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+
+// r = a + b (256-bit, no carry out expected)
+PSD_DEV void add8(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %8, %16;\n\t"
+        "addc.cc.u32 %1, %9, %17;\n\t"
+        "addc.cc.u32 %2, %10, %18;\n\t"
+        "addc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\t"
+        "addc.cc.u32 %5, %13, %21;\n\t"
+        "addc.cc.u32 %6, %14, %22;\n\t"
+        "addc.u32 %7, %15, %23;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+#else
+    uint64_t c = 0;
+    for (int k = 0; k < 8; k++) {
+        uint64_t s = (uint64_t)a[k] + b[k] + c;
+        r[k] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+
+// r = (a >= p) ? a - p : a      (a < 2p)
+template <class F>
+PSD_DEV void cond_sub_p(uint32_t* r, const uint32_t* a) {
+    uint32_t d[8];
+    uint32_t borrow;
+#if !defined(PSD_HOST_EMU)
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]),
+          "=r"(borrow)
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]),
+          "n"(F::P0), "n"(F::P1), "n"(F::P2), "n"(F::P3), "n"(F::P4), "n"(F::P5), "n"(F::P6), "n"(F::P7));
+#else
+    const uint32_t p[8] = {F::P0, F::P1, F::P2, F::P3, F::P4, F::P5, F::P6, F::P7};
+    int64_t c = 0;
+    for (int k = 0; k < 8; k++) {
+        int64_t s = (int64_t)a[k] - p[k] + c;
+        d[k] = (uint32_t)s;
+        c = s >> 32;   // 0 or -1
+    }
+    borrow = (uint32_t)c;
+#endif
+#pragma unroll
+    for (int k = 0; k < 8; k++) r[k] = borrow ? a[k] : d[k];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Field operations on fully reduced Montgomery residues in [0,p).
+// ------------------------------------------------------------------------------------------------
+
+// r = a + b mod p   (ark-ff add_assign; used by apply_ark poseidon/mod.rs:76-80, the MDS sums 82-93
+// and absorb 128,143)
+template <class F>
+PSD_DEV void fp_add(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t s[8];
+    add8(s, a, b);          // a + b < 2p < 2^256 for both fields
+    cond_sub_p<F>(r, s);
+}
+
+// One CIOS row after the first: window slides, adds a*b_i, then the Montgomery step.
+// On entry x[0] == 0 (x lo-aligned, y hi-aligned); on exit y[0] == 0 with roles swapped.
+template <class F>
+PSD_DEV void mont_row(uint32_t* x, uint32_t* y, const uint32_t* a, uint32_t bi) {
+    mad4_slide(x, y[0], a[1], a[3], a[5], a[7], bi);
+    mad4(y, a[0], a[2], a[4], a[6], bi, x[7]);
+    const uint32_t m = y[0] * F::NP0;
+    mad4_nc(x, F::P1, F::P3, F::P5, F::P7, m);
+    mad4(y, F::P0, F::P2, F::P4, F::P6, m, x[7]);
+}
+
+// r = a * b * 2^-256 mod p, fully reduced.  Requires a < 2^255 (true for any residue of either
+// field), b < 2^256.  Bound: with V the running (unshifted) accumulator value,
+// V_i <= V_{i-1}/2^32 + (2^32-1)(a+p) < 2^288, so the hi-aligned accumulator (columns 1..8) never
+// carries out, and the result is < a + p <= 2p: one conditional subtraction.
+// 128 IMAD.WIDE.U32 + 8 IMAD = 136 integer multiplies (SURVEY.md 8(d) unit of work).
+template <class F>
+PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
+    uint32_t e[8], o[8];
+    mul4(e, a[0], a[2], a[4], a[6], b[0]);
+    mul4(o, a[1], a[3], a[5], a[7], b[0]);
+    const uint32_t m = e[0] * F::NP0;
+    mad4_nc(o, F::P1, F::P3, F::P5, F::P7, m);
+    mad4(e, F::P0, F::P2, F::P4, F::P6, m, o[7]);
+    mont_row<F>(e, o, a, b[1]);
+    mont_row<F>(o, e, a, b[2]);
+    mont_row<F>(e, o, a, b[3]);
+    mont_row<F>(o, e, a, b[4]);
+    mont_row<F>(e, o, a, b[5]);
+    mont_row<F>(o, e, a, b[6]);
+    mont_row<F>(e, o, a, b[7]);
+    uint32_t s[8];
+    merge8(s, e, o);        // o[0] == 0 here
+    cond_sub_p<F>(r, s);
+}
+
+// x^alpha for the S-box (apply_s_box, poseidon/mod.rs:63-74).  ark-ff's `pow` is an MSB-first
+// square-and-multiply; exponentiation is exponentiation, so any chain gives the same residue.
+template <class F>
+PSD_DEV void fp_pow5(uint32_t* r, const uint32_t* x) {
+    uint32_t x2[8], x4[8];
+    mont_mul<F>(x2, x, x);
+    mont_mul<F>(x4, x2, x2);
+    mont_mul<F>(r, x4, x);
+}
+
+template <class F>
+PSD_DEV void fp_pow_u64(uint32_t* r, const uint32_t* x, uint64_t alpha, const uint32_t* one_mont) {
+    // generic MSB-first ladder; alpha is uniform across the grid
+    uint32_t acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) acc[k] = one_mont[k];
+    bool started = false;
+#pragma unroll 1
+    for (int bit = 63; bit >= 0; bit--) {
+        if (started) mont_mul<F>(acc, acc, acc);
+        if ((alpha >> bit) & 1) {
+            if (started) {
+                mont_mul<F>(acc, acc, x);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; k++) acc[k] = x[k];
+                started = true;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) r[k] = acc[k];
+}
+
+}  // namespace psd

@@ -1,0 +1,21 @@
+// Derivation of the optimised-permutation constants (host, one-time) -- see opt_constants.cpp.
+#pragma once
+#include <stdint.h>
+
+#include <vector>
+
+#include "host_field.hpp"
+#include "poseidon_core.cuh"
+
+namespace psd {
+
+// Appends the optimised-permutation constants for one parameter set (Montgomery inputs) to the
+// constant-bank image and records their image-relative offsets in `d`.
+void append_optimised_constants(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
+                                const std::vector<Fe>& ark_mont, const std::vector<Fe>& mds_mont, PermDesc& d,
+                                std::vector<uint32_t>& img);
+
+// Rebases every offset of `d` from image-relative to pool-relative.
+void offset_desc(PermDesc& d, uint32_t pool_off);
+
+}  // namespace psd

@@ -1,0 +1,222 @@
+// The sponge kernel template (sm_100a): one thread = one sponge; the t-element state lives in
+// registers for the whole call sequence.  Instantiated per (field, t) by tu_sponge.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "kernels.cuh"
+
+namespace psd {
+
+// ------------------------------------------------------------------------------------------------
+// Element load/store.  AoS: elem(i,k) at u32 offset (i*w + k)*8.  SoA: half h of elem(i,k) at u32
+// offset ((k*2+h)*n + i)*4, so a warp touches 32 consecutive 16-byte words.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_elem(uint32_t* x, const uint32_t* base, int layout, uint64_t n,
+                                          uint64_t i, uint32_t w, uint32_t k) {
+    const uint4* p0;
+    const uint4* p1;
+    if (layout == kLayoutAos) {
+        p0 = reinterpret_cast<const uint4*>(base + (i * w + k) * 8);
+        p1 = p0 + 1;
+    } else {
+        p0 = reinterpret_cast<const uint4*>(base + ((uint64_t)(k * 2) * n + i) * 4);
+        p1 = reinterpret_cast<const uint4*>(base + ((uint64_t)(k * 2 + 1) * n + i) * 4);
+    }
+    const uint4 a = __ldg(p0);
+    const uint4 b = __ldg(p1);
+    x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w;
+    x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+}
+
+__device__ __forceinline__ void store_elem(const uint32_t* x, uint32_t* base, int layout, uint64_t n,
+                                           uint64_t i, uint32_t w, uint32_t k) {
+    uint4* p0;
+    uint4* p1;
+    if (layout == kLayoutAos) {
+        p0 = reinterpret_cast<uint4*>(base + (i * w + k) * 8);
+        p1 = p0 + 1;
+    } else {
+        p0 = reinterpret_cast<uint4*>(base + ((uint64_t)(k * 2) * n + i) * 4);
+        p1 = reinterpret_cast<uint4*>(base + ((uint64_t)(k * 2 + 1) * n + i) * 4);
+    }
+    *p0 = make_uint4(x[0], x[1], x[2], x[3]);
+    *p1 = make_uint4(x[4], x[5], x[6], x[7]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The sponge kernel.  VARIANT selects the permutation implementation (0 = dense/reference order).
+// ------------------------------------------------------------------------------------------------
+template <class F, int T, int ALPHA, int VARIANT>
+__device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d) {
+    if constexpr (T > 5) {
+        permute_rolled<F, T, ALPHA>(st, d);
+    } else {
+        permute_dense<F, T, ALPHA>(st, d);
+    }
+}
+
+template <class F, int T, int ALPHA, int VARIANT>
+__global__ void __launch_bounds__(128) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+    const PermDesc& d = a.d;
+    const uint32_t rate = d.rate, cap = d.capacity;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    bool bad = false;
+
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+        uint32_t st[T][8];
+        if (a.state_in != nullptr) {
+#pragma unroll
+            for (int l = 0; l < T; l++) {
+                load_elem(st[l], a.state_in, a.state_in_layout, a.n, i, T, l);
+                if (a.state_in_repr == kReprCanonical) {
+                    bad |= !is_canonical<F>(st[l]);
+                    to_mont<F>(st[l], d);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int l = 0; l < T; l++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) st[l][k] = 0;
+        }
+
+        // Warp-uniform sequencer with a single permutation site.
+        int stage = 0;
+        int mode = a.mode;
+        uint32_t idx = a.index;
+        uint32_t rem_raw = a.n_raw;
+        uint32_t rem_in = a.n_absorb, k_in = 0;
+        uint32_t rem_out = a.n_squeeze, k_out = 0;
+        for (;;) {
+            bool perm = false;
+            uint32_t add_cnt = 0, emit_cnt = 0, lane0 = 0;
+            switch (stage) {
+                case 0:   // raw permutations
+                    if (rem_raw) {
+                        rem_raw--;
+                        perm = true;
+                    } else {
+                        stage = 1;
+                    }
+                    break;
+                case 1:   // CryptographicSponge::absorb entry, mod.rs:232-254
+                    if (a.n_absorb == 0) {
+                        stage = 3;
+                        break;
+                    }
+                    if (mode == kModeAbsorbing) {
+                        if (idx == rate) {
+                            perm = true;
+                            idx = 0;
+                        }
+                    } else {
+                        perm = true;
+                        idx = 0;
+                    }
+                    mode = kModeAbsorbing;
+                    stage = 2;
+                    break;
+                case 2:   // absorb_internal, mod.rs:121-150
+                    lane0 = cap + idx;
+                    if (idx + rem_in <= rate) {
+                        add_cnt = rem_in;
+                        idx += rem_in;
+                        stage = 3;
+                    } else {
+                        add_cnt = rate - idx;
+                        idx = 0;
+                        perm = true;
+                    }
+                    break;
+                case 3:   // squeeze_native_field_elements entry, mod.rs:320-342
+                    if (!a.do_squeeze) {
+                        stage = 5;
+                        break;
+                    }
+                    if (mode == kModeAbsorbing || idx == rate) {
+                        perm = true;
+                        idx = 0;
+                    }
+                    mode = kModeSqueezing;
+                    stage = 4;
+                    break;
+                case 4:   // squeeze_internal, mod.rs:153-182
+                    lane0 = cap + idx;
+                    if (idx + rem_out <= rate) {
+                        emit_cnt = rem_out;
+                        idx += rem_out;
+                        stage = 5;
+                    } else {
+                        emit_cnt = rate - idx;
+                        perm = (rem_out != rate);   // tested before the decrement, mod.rs:175
+                        idx = 0;
+                    }
+                    break;
+                default:
+                    break;
+            }
+
+            if (add_cnt) {
+#pragma unroll
+                for (int l = 0; l < T; l++) {
+                    const uint32_t j = (uint32_t)l - lane0;
+                    if ((uint32_t)l >= lane0 && j < add_cnt) {
+                        uint32_t e[8];
+                        load_elem(e, a.in, a.in_layout, a.n, i, a.n_absorb, k_in + j);
+                        if (a.in_repr == kReprCanonical) {
+                            bad |= !is_canonical<F>(e);
+                            to_mont<F>(e, d);
+                        }
+                        fp_add<F>(st[l], st[l], e);
+                    }
+                }
+                k_in += add_cnt;
+                rem_in -= add_cnt;
+            }
+            if (emit_cnt) {
+#pragma unroll
+                for (int l = 0; l < T; l++) {
+                    const uint32_t j = (uint32_t)l - lane0;
+                    if ((uint32_t)l >= lane0 && j < emit_cnt) {
+                        uint32_t e[8];
+#pragma unroll
+                        for (int k = 0; k < 8; k++) e[k] = st[l][k];
+                        if (a.out_bytes != nullptr) {
+                            // squeeze_bytes, mod.rs:256-270: first 31 LE bytes of the canonical value
+                            from_mont<F>(e);
+                            const uint32_t usable = (F::kBits - 1) / 8;
+                            const uint32_t off = (k_out + j) * usable;
+                            uint8_t* dst = a.out_bytes + i * (uint64_t)a.n_bytes + off;
+                            for (uint32_t b = 0; b < usable && off + b < a.n_bytes; b++)
+                                dst[b] = (uint8_t)(e[b >> 2] >> ((b & 3) * 8));
+                        } else {
+                            if (a.out_repr == kReprCanonical) from_mont<F>(e);
+                            store_elem(e, a.out, a.out_layout, a.n, i, a.n_squeeze, k_out + j);
+                        }
+                    }
+                }
+                k_out += emit_cnt;
+                rem_out -= emit_cnt;
+            }
+            if (perm) {
+                permute<F, T, ALPHA, VARIANT>(st, d);
+            } else if (stage == 5) {
+                break;
+            }
+        }
+
+        if (a.state_out != nullptr) {
+#pragma unroll
+            for (int l = 0; l < T; l++) {
+                uint32_t e[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) e[k] = st[l][k];
+                if (a.state_out_repr == kReprCanonical) from_mont<F>(e);
+                store_elem(e, a.state_out, a.state_out_layout, a.n, i, T, l);
+            }
+        }
+    }
+    if (bad && a.err) atomicOr(a.err, 1);
+}
+
+}  // namespace psd
