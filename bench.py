@@ -1,0 +1,427 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path: Poseidon permutations/s on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c4|c5]
+
+One "step" = one pass of the hot path over one batch of synthetic field elements (generated on the
+device with the counter-based generator of SURVEY.md 8(d)).  Default workload = BASELINE.json
+configs[1] (C2): BN254 Fr, t=3, alpha=5, RF=8, RP=57, 2^24 independent permutations per GPU, states
+AoS/Montgomery (the memory image of a Rust `&[Fr]`), 1.5 GiB in place -- far larger than the 126 MB
+L2, so no L2 flush is needed between iterations.
+
+Multi-GPU (torchrun, one rank per GPU): contiguous shards, no data-path collective ("weak" scaling:
+per-GPU work is fixed); `value` = units processed by all ranks / max-over-ranks device time.
+
+The JSON line carries `roofline` (integer-multiply pipe: algorithmic 32x32 multiplies per
+permutation x permutations / kernel time, against the K0 probe measured in the same run; the HBM
+view is given next to it), `cpu_baseline` (the C port of the reference's CPU path, oracle/, on the
+host cores, bounded sample), `e2e` (same metric through psd_permute_batch with pinned HOST
+buffers: H2D + kernel + D2H inside the timed region), `clocks`, and `gpu_launches`.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# Algorithmic work per permutation: M = (RF*t + RP)*S(alpha) + (RF+RP)*t^2 Montgomery
+# products with the reference's dense MDS, 136 32x32-bit multiplies per 8-limb CIOS product.
+IMUL_PER_MODMUL = 136
+
+
+def sbox_mults(alpha):
+    return {5: 3, 17: 5, 257: 9, 3: 2}[alpha]
+
+
+def modmuls_per_perm(t, rf, rp, alpha):
+    return (rf * t + rp) * sbox_mults(alpha) + (rf + rp) * t * t
+
+
+WORKLOADS = {
+    # name: (field, rate, rf, rp, alpha, description)
+    "c2": dict(field="bn254", rate=2, rf=8, rp=57, alpha=5, log_n=24,
+               desc="BN254 Fr t=3 (rate 2, capacity 1) alpha=5 RF=8 RP=57: 2^24 independent permutations per GPU"),
+    "c3": dict(field="bn254", rate=4, rf=8, rp=60, alpha=5, log_n=24,
+               desc="BN254 Fr t=5 (rate 4) alpha=5 RF=8 RP=60: 2^24 absorb-4/squeeze-1 hashes per GPU"),
+    "c4": dict(field="bn254", rate=2, rf=8, rp=57, alpha=5, log_n=23,
+               desc="Poseidon Merkle tree, BN254 t=3: 2^23-leaf subtree per GPU, roots gathered for the top levels"),
+    "c5": dict(field="bls12_381", rate=2, rf=8, rp=29, alpha=17, log_n=20,
+               desc="BLS12-381 Fr fixture params: 2^20 sponges per GPU absorb 1024 elements, squeeze_bytes(32)"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--log-n", type=int, default=None, help="override log2(units per GPU)")
+    ap.add_argument("--variant", type=int, default=1, help="0 = dense kernel, 1 = optimised kernel")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target duration of the CPU baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# parameters for both arms
+# ------------------------------------------------------------------------------------------------
+def oracle_config(w):
+    from oracle import poseidon_ref as R
+    if w["field"] == "bn254":
+        return R.bn254_config(w["rate"], w["rf"], w["rp"], w["alpha"]), 0
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "bls12_381_fixture_params.json")))
+    return R.PoseidonConfig(fx["full_rounds"], fx["partial_rounds"], fx["alpha"],
+                            [[int(v) for v in r] for r in fx["mds"]], [[int(v) for v in r] for r in fx["ark"]],
+                            fx["rate"], fx["capacity"], R.BLS12_381_FR), 1
+
+
+def product_config(w):
+    """Parameters for the product arm come from the library's own generator (no oracle)."""
+    import sponge_b200 as S
+    if w["field"] == "bn254":
+        ark, mds = S.find_poseidon_ark_and_mds("bn254", 254, w["rate"], w["rf"], w["rp"], 0)
+        return S.PoseidonConfig.new(w["rf"], w["rp"], w["alpha"], mds, ark, w["rate"], 1, "bn254")
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "bls12_381_fixture_params.json")))
+    return S.PoseidonConfig.new(fx["full_rounds"], fx["partial_rounds"], fx["alpha"],
+                                [[int(v) for v in r] for r in fx["mds"]], [[int(v) for v in r] for r in fx["ark"]],
+                                fx["rate"], fx["capacity"], "bls12_381")
+
+
+def units_and_perms(name, w, n):
+    """(units per step per GPU, permutations per unit)."""
+    if name == "c4":
+        return n - 1, 1          # compressions in a subtree of n leaves
+    if name == "c5":
+        return n, 512            # 511 absorb permutes + 1 squeeze permute per sponge
+    return n, 1
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the C port of the reference's CPU path on the host cores (bounded sample)
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(name, w, seconds, threads=0):
+    from oracle.c_oracle import COracle
+    ocfg, fid = oracle_config(w)
+    orc = COracle(ocfg, fid)
+    cores = orc.max_threads() if threads <= 0 else threads
+    t = w["rate"] + 1
+
+    def run(n):
+        if name == "c2":
+            st = orc.synth(n * t, seed=0xC2)
+            t0 = time.perf_counter()
+            orc.permute_batch(st, threads)
+            return time.perf_counter() - t0, n
+        if name == "c3":
+            x = orc.synth(n * 4, seed=0xC3)
+            t0 = time.perf_counter()
+            orc.absorb_squeeze_batch(x, n, 4, 1, threads)
+            return time.perf_counter() - t0, n
+        if name == "c4":
+            x = orc.synth(n, seed=0xC4)
+            t0 = time.perf_counter()
+            orc.merkle_root(x, threads)
+            return time.perf_counter() - t0, n - 1
+        x = orc.synth(n * 1024, seed=0xC5)
+        t0 = time.perf_counter()
+        orc.absorb_squeeze_bytes_batch(x, n, 1024, 32, threads)
+        return time.perf_counter() - t0, n * 512
+
+    probe = 1 << (10 if name == "c5" else 15)
+    dt, units = run(probe)
+    rate = units / dt
+    n = probe
+    while n * 2 * (512 if name == "c5" else 1) / rate <= seconds and n < (1 << 22):
+        n *= 2
+    dt, units = run(n)
+    return dict(value=units / dt, unit="perm/s", cores=cores, kind="port",
+                sample=f"{n} {'sponges x 512 perms' if name == 'c5' else 'units'} of workload {name} "
+                       f"({dt:.1f} s, OpenMP over independent sponges)")
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons, power = [], None, set(), []
+        for ts, line in self.rows:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 8 or not (t0 <= ts <= t1 + 0.15):
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx = float(parts[2])
+                power.append(float(parts[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons),
+                    samples=len(sm), power_w_max=max(power) if power else None)
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    name = args.workload
+    w = WORKLOADS[name]
+    log_n = args.log_n if args.log_n is not None else w["log_n"]
+    n = 1 << log_n
+    t = w["rate"] + 1
+
+    if args.impl == "reference":
+        # The reference's own CPU implementation cannot be built here (Rust, ark-ff not vendored), so this
+        # arm times the C port of it (oracle/) on all host threads, rank 0 only, bounded sample per step.
+        if rank != 0:
+            return
+        best = None
+        vals = []
+        per_step = max(2.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
+        for i in range(args.warmup + args.steps):
+            r = cpu_baseline(name, w, per_step)
+            if i >= args.warmup:
+                vals.append(r["value"])
+                best = r
+        value = sum(vals) / len(vals)
+        best["value"] = value
+        line = dict(impl="reference", metric="poseidon_permutations_per_second", value=value, unit="perm/s",
+                    n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=None, higher_is_better=True,
+                    scaling="weak", vs_baseline=None, dtype="u32x8 (256-bit Montgomery, 4x64-bit limbs on CPU)",
+                    data="synthetic", config=dict(workload=f"{name}: {w['desc']}", sample=best["sample"]),
+                    cpu_baseline=best,
+                    e2e=dict(value=value, unit="perm/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        print(json.dumps(line))
+        return
+
+    import numpy as np
+    import torch
+    import sponge_b200 as S
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product arm has no CPU path (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    cfg = product_config(w)
+    ctx = cfg.context(local_rank)
+    ctx.set_variant(args.variant)
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+    units, perms_per_unit = units_and_perms(name, w, n)
+
+    # ---- device-resident inputs --------------------------------------------------------------------
+    seed = {"c2": 0xC2, "c3": 0xC3, "c4": 0xC4, "c5": 0xC5}[name]
+    first = rank * n   # each rank owns a contiguous shard of the global index space
+    if name == "c2":
+        buf = torch.empty((n * t, 4), dtype=torch.int64, device="cuda")
+        ctx.synth_fill_dev(buf.data_ptr(), n * t, seed, first * t, stream=sptr)
+
+        def step():
+            ctx.permute_batch_dev(buf.data_ptr(), n, stream=sptr)
+        launches_per_step = 1
+        alg_bytes = n * t * 32 * 2
+    elif name == "c3":
+        buf = torch.empty((n * 4, 4), dtype=torch.int64, device="cuda")
+        out = torch.empty((n, 4), dtype=torch.int64, device="cuda")
+        ctx.synth_fill_dev(buf.data_ptr(), n * 4, seed, first * 4, stream=sptr)
+
+        def step():
+            ctx.absorb_squeeze_batch_dev(buf.data_ptr(), n, 4, 1, out.data_ptr(), stream=sptr)
+        launches_per_step = 1
+        alg_bytes = n * 5 * 32
+    elif name == "c4":
+        buf = torch.empty((n, 4), dtype=torch.int64, device="cuda")
+        root = torch.empty((1, 4), dtype=torch.int64, device="cuda")
+        ctx.synth_fill_dev(buf.data_ptr(), n, seed, first, stream=sptr)
+        roots = torch.empty((world, 4), dtype=torch.int64, device="cuda") if world > 1 else None
+        top = torch.empty((1, 4), dtype=torch.int64, device="cuda")
+
+        def step():
+            ctx.merkle_root_dev(buf.data_ptr(), n, root.data_ptr(), stream=sptr)
+            if world > 1:
+                # the one exchange step of the path: world x 32-byte subtree roots to every rank
+                dist.all_gather_into_tensor(roots, root)
+                if rank == 0:
+                    ctx.merkle_root_dev(roots.data_ptr(), world, top.data_ptr(), stream=sptr)
+        launches_per_step = log_n
+        alg_bytes = n * 32 * 3 // 2
+    else:
+        chunk = 64   # elements absorbed per call; inputs regenerated on the device chunk by chunk
+        buf = torch.empty((n * chunk, 4), dtype=torch.int64, device="cuda")
+        outb = torch.empty((n, 32), dtype=torch.uint8, device="cuda")
+        ctx.synth_fill_dev(buf.data_ptr(), n * chunk, seed, first * chunk, stream=sptr)
+
+        def step():
+            b = S.SpongeBatch(ctx, n)
+            for _ in range(1024 // chunk):
+                b.absorb_dev(buf.data_ptr(), chunk)
+            b.squeeze_bytes_dev(32, outb.data_ptr())
+            b.free()
+        launches_per_step = 1024 // chunk + 1
+        alg_bytes = n * 1024 * 32
+    ctx.synchronize(sptr)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- K0: integer-multiply peak of this box, measured in this run ----------------------------------
+    imad_wide, _ = ctx.imad_peak(0)
+    imad_lo, _ = ctx.imad_peak(1)
+    modmul_rate, _ = ctx.imad_peak(2)
+
+    # ---- warm-up + timed region (device-resident) -----------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    launches0 = S.kernel_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    ev[0].record(stream)
+    for i in range(args.steps):
+        step()
+        ev[i + 1].record(stream)
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = S.kernel_launch_count() - launches0
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per_step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    if dist is not None:
+        tt = torch.tensor([total_ms], device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms = float(tt.item())
+    ms_per_step = total_ms / args.steps
+    value = units * perms_per_unit * world / (ms_per_step * 1e-3)
+
+    # ---- e2e: public API with pinned HOST buffers, H2D + kernel + D2H inside the timed region ------------
+    e2e = None
+    if not args.no_e2e and name in ("c2", "c3"):
+        in_el = n * t if name == "c2" else n * 4
+        out_el = n * t if name == "c2" else n
+        h_in = torch.empty((in_el, 4), dtype=torch.int64).pin_memory()
+        h_in.copy_(buf.cpu())
+        h_out = h_in if name == "c2" else torch.empty((out_el, 4), dtype=torch.int64).pin_memory()
+        a_in = h_in.numpy().view(np.uint64)
+        a_out = h_out.numpy().view(np.uint64)
+        from sponge_b200._lib import lib, check, LAYOUT_AOS, REPR_MONTGOMERY, MEM_HOST
+
+        def e2e_step():
+            if name == "c2":
+                check(lib.psd_permute_batch(ctx.handle, a_in.ctypes.data, n, LAYOUT_AOS, REPR_MONTGOMERY, MEM_HOST, None))
+            else:
+                check(lib.psd_absorb_squeeze_batch(ctx.handle, a_in.ctypes.data, n, 4, 1, a_out.ctypes.data,
+                                                   LAYOUT_AOS, REPR_MONTGOMERY, MEM_HOST, None))
+        e2e_steps = max(2, min(args.steps, 5))
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()   # returns when the outputs are in host memory
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            tt = torch.tensor([dt], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+        e2e = dict(value=units * world * e2e_steps / dt, unit="perm/s", h2d_bytes_per_step=in_el * 32,
+                   d2h_bytes_per_step=out_el * 32, steps=e2e_steps,
+                   note="psd_permute_batch/psd_absorb_squeeze_batch with PSD_MEM_HOST on pinned buffers; "
+                        "wall clock around blocking calls")
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline ------------------------------------------------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"
+    mm = modmuls_per_perm(t, w["rf"], w["rp"], w["alpha"])
+    w_alg = mm * IMUL_PER_MODMUL
+    launch_ms = ms_per_step / launches_per_step if name in ("c2", "c3") else ms_per_step
+    perms_per_step_gpu = units * perms_per_unit
+    achieved_imul = perms_per_step_gpu * w_alg / (ms_per_step * 1e-3)
+    roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_wide / 1e9, unit="Gimul/s",
+                    frac=achieved_imul / imad_wide, traffic=None,
+                    w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
+                    peak_source="K0 probe in this run: sustained IMAD.WIDE.U32 results/s on all SMs",
+                    k0=dict(imad_wide_per_s=imad_wide, imad_lo_per_s=imad_lo, mont_mul_per_s=modmul_rate,
+                            mont_mul_imul_per_s=modmul_rate * IMUL_PER_MODMUL),
+                    kernel_ms=launch_ms,
+                    hbm=dict(achieved=alg_bytes / (ms_per_step * 1e-3) / 1e9, peak=hbm_peak, unit="GB/s",
+                             frac=alg_bytes / (ms_per_step * 1e-3) / 1e9 / hbm_peak, peak_source=hbm_src,
+                             algorithmic_bytes_per_step=alg_bytes))
+
+    cpu = None
+    if not args.no_cpu and world == 1:
+        cpu = cpu_baseline(name, w, args.cpu_seconds)
+
+    line = dict(metric="poseidon_permutations_per_second", value=value, unit="perm/s", n_gpus=world, steps=args.steps,
+                warmup=max(args.warmup, 3), ms_per_step=ms_per_step, higher_is_better=True, scaling="weak",
+                vs_baseline=None, dtype="u32x8 (256-bit Montgomery residues, 8x32-bit limbs)", data="synthetic",
+                config=dict(workload=f"{name}: {w['desc']}", units_per_gpu_per_step=units,
+                            permutations_per_unit=perms_per_unit, kernel_variant=args.variant,
+                            layout="AoS Montgomery, device-resident, in place",
+                            l2="inputs larger than L2 (no flush needed)" if alg_bytes > (252 << 20) else "inputs fit L2",
+                            per_step_ms=[round(x, 4) for x in per_step_ms]),
+                roofline=roofline, cpu_baseline=cpu, e2e=e2e, clocks=clocks, gpu_launches=int(launches))
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
