@@ -48,7 +48,7 @@ if newer oracle/liboracle.so oracle/poseidon_oracle.c; then
   gcc -O3 -fopenmp -shared -fPIC -o oracle/liboracle.so oracle/poseidon_oracle.c
 fi
 # host emulation of the device arithmetic (test infrastructure)
-if newer tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $HDRS; then
-  g++ -O2 -std=c++17 -shared -fPIC -o tests/emu/libfp_emu.so tests/emu/fp_emu.cpp
+if newer tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $SRC/opt_constants.cpp $SRC/params.cpp $HDRS; then
+  g++ -O2 -std=c++17 -shared -fPIC -o tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $SRC/opt_constants.cpp $SRC/params.cpp
 fi
 echo "built $LIB/libposeidon_b200.so"

@@ -223,7 +223,8 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
 }
 
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
-    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, ctx->variant);
+    const int variant = (ctx->variant == 1 && ctx->desc.opt_ok) ? 1 : 0;
+    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
     LaunchCfg cfg = sponge_cfg(ctx, k, a.n);
@@ -502,7 +503,9 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     d.capacity = p->capacity;
     d.alpha_lo = (uint32_t)p->alpha;
     d.alpha_hi = (uint32_t)(p->alpha >> 32);
-    append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
+    // optimised-form constants only where an optimised kernel exists (t <= 5)
+    if (t <= 5)
+        append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
 
     DeviceGuard guard(device);
     if (!guard.ok) {

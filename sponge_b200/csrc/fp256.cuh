@@ -57,14 +57,18 @@ struct Bls12381Fr {
 // d[2k],d[2k+1] = a_k * b   (four independent 32x32->64 products)
 PSD_DEV void mul4(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b) {
 #if !defined(PSD_HOST_EMU)
-    asm("mul.lo.u32 %0, %8, %12;\n\t"
-        "mul.hi.u32 %1, %8, %12;\n\t"
-        "mul.lo.u32 %2, %9, %12;\n\t"
-        "mul.hi.u32 %3, %9, %12;\n\t"
-        "mul.lo.u32 %4, %10, %12;\n\t"
-        "mul.hi.u32 %5, %10, %12;\n\t"
-        "mul.lo.u32 %6, %11, %12;\n\t"
-        "mul.hi.u32 %7, %11, %12;"
+    // mul.wide + unpack keeps each product a single IMAD.WIDE.U32 (mul.lo/mul.hi pairs are not fused)
+    asm("{\n\t"
+        ".reg .u64 t0, t1, t2, t3;\n\t"
+        "mul.wide.u32 t0, %8, %12;\n\t"
+        "mul.wide.u32 t1, %9, %12;\n\t"
+        "mul.wide.u32 t2, %10, %12;\n\t"
+        "mul.wide.u32 t3, %11, %12;\n\t"
+        "mov.b64 {%0, %1}, t0;\n\t"
+        "mov.b64 {%2, %3}, t1;\n\t"
+        "mov.b64 {%4, %5}, t2;\n\t"
+        "mov.b64 {%6, %7}, t3;\n\t"
+        "}"
         : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
 #else
@@ -291,6 +295,55 @@ PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     merge8(s, e, o);        // o[0] == 0 here
     cond_sub_p<F>(r, s);
 }
+
+// r = (sum_{j<N} a[j] * b[j]) * 2^-256 mod p with ONE interleaved Montgomery reduction ("lazy"
+// MDS row): N*64 + 64 wide multiplies instead of N*128.  Requires every a[j] < p and
+// (N+1)*p < 2^256, which keeps the running window below 2^288 (same argument as mont_mul with
+// N+1 addends of size < p*2^32 per row), so the hi-aligned accumulator never carries out; the
+// result is < p*(1 + N*p/2^256) < 2p: one conditional subtraction.
+//   BN254 Fr: N <= 4.   BLS12-381 Fr: N = 1 only (use mont_mul).
+template <class F, int N>
+PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8]) {
+    uint32_t e[8], o[8];
+    // row 0
+    mul4(e, a[0][0], a[0][2], a[0][4], a[0][6], b[0][0]);
+    mul4(o, a[0][1], a[0][3], a[0][5], a[0][7], b[0][0]);
+#pragma unroll
+    for (int j = 1; j < N; j++) {
+        mad4_nc(o, a[j][1], a[j][3], a[j][5], a[j][7], b[j][0]);
+        mad4(e, a[j][0], a[j][2], a[j][4], a[j][6], b[j][0], o[7]);
+    }
+    {
+        const uint32_t m = e[0] * F::NP0;
+        mad4_nc(o, F::P1, F::P3, F::P5, F::P7, m);
+        mad4(e, F::P0, F::P2, F::P4, F::P6, m, o[7]);
+    }
+    // rows 1..7: x = accumulator whose column 0 is now zero, y = the other one
+#pragma unroll
+    for (int i = 1; i < 8; i++) {
+        uint32_t* x = (i & 1) ? e : o;
+        uint32_t* y = (i & 1) ? o : e;
+        mad4_slide(x, y[0], a[0][1], a[0][3], a[0][5], a[0][7], b[0][i]);
+        mad4(y, a[0][0], a[0][2], a[0][4], a[0][6], b[0][i], x[7]);
+#pragma unroll
+        for (int j = 1; j < N; j++) {
+            mad4_nc(x, a[j][1], a[j][3], a[j][5], a[j][7], b[j][i]);
+            mad4(y, a[j][0], a[j][2], a[j][4], a[j][6], b[j][i], x[7]);
+        }
+        const uint32_t m = y[0] * F::NP0;
+        mad4_nc(x, F::P1, F::P3, F::P5, F::P7, m);
+        mad4(y, F::P0, F::P2, F::P4, F::P6, m, x[7]);
+    }
+    uint32_t s[8];
+    merge8(s, e, o);        // after row 7: o[0] == 0
+    cond_sub_p<F>(r, s);
+}
+
+// Largest N for which mont_dot's no-overflow condition (N+1)*p < 2^256 holds.
+template <class F>
+struct DotLimit {
+    static constexpr int kMax = (F::kBits == 254) ? 4 : 1;
+};
 
 // x^alpha for the S-box (apply_s_box, poseidon/mod.rs:63-74).  ark-ff's `pow` is an MSB-first
 // square-and-multiply; exponentiation is exponentiation, so any chain gives the same residue.

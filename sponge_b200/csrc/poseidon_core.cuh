@@ -33,6 +33,11 @@ struct PermDesc {
     uint32_t rate;
     uint32_t capacity;
     uint32_t alpha_lo, alpha_hi;
+    // optimised form (see opt_constants.cpp); valid when opt_ok != 0
+    uint32_t opt_ok;
+    uint32_t pre_mds_off;   // [T][T][8]  matrix of the last full round before the partial rounds
+    uint32_t sparse_off;    // [partial][2T-1][8]: k, w_1..w_{T-1}, v_1..v_{T-1} per partial round
+    uint32_t post_ark_off;  // [T][8]     round constants of the first full round after the partial rounds
 };
 
 template <class F, int ALPHA>
@@ -106,6 +111,131 @@ PSD_DEV void permute_dense(uint32_t (&st)[T][8], const PermDesc& d) {
     for (uint32_t r = 0; r < d.total; r++) {
         const bool full = (r < d.half_full) || (r >= d.half_full + d.partial);
         round_dense<F, T, ALPHA>(st, d, r, full);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Optimised permutation: same function, fewer multiplier-pipe cycles.
+//  * partial rounds in sparse form: the MDS matrix is factored (host, once) so that a partial round
+//    is   s0 <- (s0 + k)^alpha ;  s0' = M00*s0 + sum_j w_j*s_j ;  s_j' = s_j + v_j*s0   (2T-1 products
+//    instead of T^2, one round constant instead of T);
+//  * every matrix row is a lazily reduced dot product (mont_dot) where the field allows it.
+// Results are identical to permute_dense: the values are the same field elements, fully reduced.
+// ------------------------------------------------------------------------------------------------
+template <class F, int T>
+PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
+    // r = sum_{j<T} st[j] * c_pool[coeff_off + 8j ...], in groups of at most DotLimit<F>::kMax terms
+    constexpr int G = DotLimit<F>::kMax;
+    bool first = true;
+#pragma unroll
+    for (int j0 = 0; j0 < T; j0 += G) {
+        uint32_t part[8];
+        uint32_t cf[G][8];
+#pragma unroll
+        for (int j = 0; j < G; j++)
+#pragma unroll
+            for (int k = 0; k < 8; k++) cf[j][k] = (j0 + j < T) ? c_pool[coeff_off + (j0 + j) * 8 + k] : 0u;
+        const int n = (T - j0 < G) ? (T - j0) : G;
+        if (n == 1) mont_mul<F>(part, st[j0], cf[0]);
+        else if (n == 2) mont_dot<F, 2>(part, st + j0, cf);
+        else if (n == 3) mont_dot<F, 3>(part, st + j0, cf);
+        else mont_dot<F, (G >= 4 ? 4 : 1)>(part, st + j0, cf);
+        if (first) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) r[k] = part[k];
+            first = false;
+        } else {
+            fp_add<F>(r, r, part);
+        }
+    }
+}
+
+template <class F, int T, int ALPHA>
+PSD_DEV void full_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t ark_off, uint32_t mds_off) {
+#pragma unroll
+    for (int i = 0; i < T; i++) {
+        uint32_t c[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) c[k] = c_pool[ark_off + i * 8 + k];
+        fp_add<F>(st[i], st[i], c);
+        sbox<F, ALPHA>(st[i], d);
+    }
+    uint32_t nw[T][8];
+#pragma unroll
+    for (int i = 0; i < T; i++) row_dot<F, T>(nw[i], st, mds_off + i * T * 8);
+#pragma unroll
+    for (int i = 0; i < T; i++)
+#pragma unroll
+        for (int k = 0; k < 8; k++) st[i][k] = nw[i][k];
+}
+
+template <class F, int T, int ALPHA>
+PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t off) {
+    // off -> [k][w_1..w_{T-1}][v_1..v_{T-1}]
+    {
+        uint32_t c[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) c[k] = c_pool[off + k];
+        fp_add<F>(st[0], st[0], c);
+        sbox<F, ALPHA>(st[0], d);
+    }
+    // s0' = M00*s0 + sum w_j s_j  : coefficients (M00, w_1, ...) -- M00 is mds[0][0]
+    uint32_t n0[8];
+    {
+        constexpr int G = DotLimit<F>::kMax;
+        bool first = true;
+#pragma unroll
+        for (int j0 = 0; j0 < T; j0 += G) {
+            uint32_t part[8];
+            uint32_t cf[G][8];
+#pragma unroll
+            for (int j = 0; j < G; j++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int jj = j0 + j;
+                    cf[j][k] = (jj >= T) ? 0u : (jj == 0 ? c_pool[d.mds_off + k] : c_pool[off + jj * 8 + k]);
+                }
+            const int n = (T - j0 < G) ? (T - j0) : G;
+            if (n == 1) mont_mul<F>(part, st[j0], cf[0]);
+            else if (n == 2) mont_dot<F, 2>(part, st + j0, cf);
+            else if (n == 3) mont_dot<F, 3>(part, st + j0, cf);
+            else mont_dot<F, (G >= 4 ? 4 : 1)>(part, st + j0, cf);
+            if (first) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) n0[k] = part[k];
+                first = false;
+            } else {
+                fp_add<F>(n0, n0, part);
+            }
+        }
+    }
+    // s_j' = s_j + v_j * s0
+#pragma unroll
+    for (int j = 1; j < T; j++) {
+        uint32_t v[8], prod[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = c_pool[off + (T - 1 + j) * 8 + k];
+        mont_mul<F>(prod, st[0], v);
+        fp_add<F>(st[j], st[j], prod);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) st[0][k] = n0[k];
+}
+
+template <class F, int T, int ALPHA>
+PSD_DEV void permute_opt(uint32_t (&st)[T][8], const PermDesc& d) {
+    const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (uint32_t r = 0; r < d.total; r++) {
+        if (r < first_partial || r >= first_post) {
+            const uint32_t ark = (r == first_post && d.partial) ? d.post_ark_off : d.ark_off + r * T * 8;
+            const uint32_t mds = (r + 1 == first_partial && d.partial) ? d.pre_mds_off : d.mds_off;
+            full_round_opt<F, T, ALPHA>(st, d, ark, mds);
+        } else {
+            partial_round_opt<F, T, ALPHA>(st, d, d.sparse_off + (r - first_partial) * (2 * T - 1) * 8);
+        }
     }
 }
 

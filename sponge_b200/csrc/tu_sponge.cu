@@ -32,11 +32,16 @@ static ConstPoolRegistrar g_pool(tu_upload);
         "sponge_kernel<" PSD_TU_FNAME ",t=" PSD_STR(PSD_TU_T) ",alpha=" #ALPHA ",variant=" #VARIANT ">"});
 
 PSD_REG(0, 0)
+#if PSD_TU_T <= 5
+PSD_REG(0, 1)
+#endif
 #if PSD_TU_T == 3 || PSD_TU_T == 5
 PSD_REG(5, 0)
+PSD_REG(5, 1)
 #endif
 #if PSD_TU_T == 3
 PSD_REG(17, 0)
+PSD_REG(17, 1)
 #endif
 
 }  // namespace psd

@@ -4,6 +4,7 @@
 #define PSD_HOST_EMU 1
 #include "../../sponge_b200/csrc/fp256.cuh"
 #include <stddef.h>
+#include <string.h>
 
 using namespace psd;
 
@@ -26,4 +27,87 @@ void emu_pow(int field, uint32_t* r, const uint32_t* a, uint64_t alpha, const ui
         else fp_pow_u64<Bls12381Fr>(r + 8 * i, a + 8 * i, alpha, one);
     }
 }
+}
+
+extern "C" void emu_mont_dot(int n_terms, uint32_t* r, const uint32_t* a, const uint32_t* b, size_t n) {
+    // BN254 only (the no-overflow bound needs (N+1)p < 2^256); a, b: n * n_terms * 8 words
+    for (size_t i = 0; i < n; i++) {
+        const uint32_t(*ap)[8] = reinterpret_cast<const uint32_t(*)[8]>(a + i * n_terms * 8);
+        const uint32_t(*bp)[8] = reinterpret_cast<const uint32_t(*)[8]>(b + i * n_terms * 8);
+        switch (n_terms) {
+            case 1: mont_dot<Bn254Fr, 1>(r + 8 * i, ap, bp); break;
+            case 2: mont_dot<Bn254Fr, 2>(r + 8 * i, ap, bp); break;
+            case 3: mont_dot<Bn254Fr, 3>(r + 8 * i, ap, bp); break;
+            case 4: mont_dot<Bn254Fr, 4>(r + 8 * i, ap, bp); break;
+        }
+    }
+}
+
+// ---- whole permutation on the host model (dense vs optimised), constants from the product's own
+// host code (params.cpp / opt_constants.cpp) ------------------------------------------------------
+#include <vector>
+
+#include "../../sponge_b200/csrc/opt_constants.hpp"
+#include "../../sponge_b200/csrc/poseidon_core.cuh"
+
+template <class F, int T, int ALPHA>
+static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        uint32_t s[T][8];
+        memcpy(s, st + i * T * 8, sizeof s);
+        if (variant == 1 && d.opt_ok) permute_opt<F, T, ALPHA>(s, d);
+        else if (variant == 2) permute_rolled<F, T, ALPHA>(s, d);
+        else permute_dense<F, T, ALPHA>(s, d);
+        memcpy(st + i * T * 8, s, sizeof s);
+    }
+}
+template <class F, int T>
+static void emu_perm_a(const PermDesc& d, uint64_t alpha, int variant, uint32_t* st, size_t n) {
+    if (alpha == 5) emu_perm_t<F, T, 5>(d, variant, st, n);
+    else if (alpha == 17) emu_perm_t<F, T, 17>(d, variant, st, n);
+    else emu_perm_t<F, T, 0>(d, variant, st, n);
+}
+template <class F>
+static int emu_perm_f(const PermDesc& d, uint32_t t, uint64_t alpha, int variant, uint32_t* st, size_t n) {
+    switch (t) {
+        case 2: emu_perm_a<F, 2>(d, alpha, variant, st, n); return 0;
+        case 3: emu_perm_a<F, 3>(d, alpha, variant, st, n); return 0;
+        case 4: emu_perm_a<F, 4>(d, alpha, variant, st, n); return 0;
+        case 5: emu_perm_a<F, 5>(d, alpha, variant, st, n); return 0;
+        case 9: emu_perm_a<F, 9>(d, alpha, variant, st, n); return 0;
+    }
+    return -1;
+}
+
+// returns 0 ok, -1 unsupported t, 1 if the optimised form was requested but is not available
+extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, uint64_t alpha,
+                           const uint64_t* ark_canon, const uint64_t* mds_canon, int variant, uint32_t* states,
+                           size_t n) {
+    const HostField* hf = host_field(field);
+    const uint32_t t = rate + capacity, rounds = rf + rp;
+    std::vector<Fe> ark(rounds * t), mds(t * t);
+    for (size_t i = 0; i < ark.size(); i++) ark[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(ark_canon)[i]);
+    for (size_t i = 0; i < mds.size(); i++) mds[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(mds_canon)[i]);
+    std::vector<uint32_t> img;
+    auto push = [&img](const Fe& f) {
+        for (int k = 0; k < 4; k++) { img.push_back((uint32_t)f.v[k]); img.push_back((uint32_t)(f.v[k] >> 32)); }
+    };
+    PermDesc d{};
+    d.ark_off = 0;
+    for (auto& f : ark) push(f);
+    d.mds_off = (uint32_t)img.size();
+    for (auto& f : mds) push(f);
+    d.one_off = (uint32_t)img.size();
+    push(hf_one(*hf));
+    d.r2_off = (uint32_t)img.size();
+    Fe r2; memcpy(r2.v, hf->r2, 32); push(r2);
+    d.half_full = rf / 2; d.partial = rp; d.total = rounds; d.rate = rate; d.capacity = capacity;
+    d.alpha_lo = (uint32_t)alpha; d.alpha_hi = (uint32_t)(alpha >> 32);
+    append_optimised_constants(*hf, t, rf, rp, ark, mds, d, img);
+    if (img.size() > kConstPoolWords) return -2;
+    memcpy(c_pool, img.data(), img.size() * 4);
+    int rc = field == 0 ? emu_perm_f<Bn254Fr>(d, t, alpha, variant, states, n)
+                        : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
+    if (rc) return rc;
+    return (variant == 1 && !d.opt_ok) ? 1 : 0;
 }

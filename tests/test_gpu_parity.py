@@ -42,7 +42,7 @@ def pairs(S, ref):
 
     def get(name):
         if name not in cache:
-            if len(cache) >= 4:   # the constant bank holds only a few parameter sets at once
+            while len(cache) >= 2:   # the 62 KiB constant bank holds only a few parameter sets at once
                 old = next(iter(cache))
                 cache.pop(old).close()
             cache[name] = Pair(S, ref, name)

@@ -1,0 +1,209 @@
+"""Host-side logic that needs no GPU: the C ABI library loads and exports every declared symbol,
+parameter generation in the library matches the reference KATs, argument/shape errors are reported
+as status codes, the device arithmetic's limb plumbing (host model) is exact, and the product
+refuses to run without a CUDA device.  No compute calls."""
+import ctypes as C
+import os
+import random
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, load_golden, oracle_cfg, to_ints, to_limbs
+
+
+@pytest.fixture(scope="module")
+def S():
+    import sponge_b200
+    return sponge_b200
+
+
+def test_library_exports_every_declared_symbol(S):
+    hdr = open(os.path.join(ROOT, "include", "poseidon_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(psd_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 45
+    lib = C.CDLL(S.LIB_PATH)
+    missing = [n for n in declared if not hasattr(lib, n)]
+    assert not missing, f"declared in include/poseidon_b200.h but not exported: {missing}"
+    # and the Python binding prototypes cover the same set
+    from sponge_b200 import _lib
+    assert sorted(_lib._PROTOS) == declared
+
+
+def test_version_and_status_strings(S):
+    from sponge_b200._lib import lib
+    assert b"sm_100a" in lib.psd_version()
+    assert lib.psd_status_string(0) == b"PSD_OK" and lib.psd_status_string(3) == b"PSD_ERR_NONCANONICAL"
+
+
+def test_library_parameter_generation_matches_reference_kats(S):
+    """psd_find_poseidon_ark_and_mds / psd_default_params (C++ Grain LFSR) vs traits.rs:163-358."""
+    entries = load_golden("reference_kats.json")["default_parameters"]["entries"]
+    for e in entries:
+        cfg = S.get_default_poseidon_parameters("bls12_381", e["rate"], e["optimized_for_weights"])
+        assert str(cfg.ark[0][0]) == e["ark00"] and str(cfg.mds[0][0]) == e["mds00"]
+        assert cfg.capacity == 1 and cfg.rate == e["rate"]
+    assert S.get_default_poseidon_parameters("bls12_381", 9, False) is None
+    assert S.get_default_poseidon_parameters("bls12_381", 1, False) is None
+
+
+def test_library_parameter_generation_matches_oracle_fully(S, ref):
+    for name, args in [("bn254_t3", ("bn254", 254, 2, 8, 57, 0)), ("bn254_t5", ("bn254", 254, 4, 8, 60, 0)),
+                       ("bls_default_r3", ("bls12_381", 255, 3, 8, 56, 0))]:
+        ark, mds = S.find_poseidon_ark_and_mds(*args)
+        o = oracle_cfg(ref, name)
+        assert ark == o.ark and mds == o.mds
+    # skip_matrices consumes 2t samples per skipped matrix
+    ark1, mds1 = S.find_poseidon_ark_and_mds("bn254", 254, 2, 8, 57, 1)
+    oark, omds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 8, 57, 1)
+    assert ark1 == oark and mds1 == omds
+    with pytest.raises(S.PoseidonB200Error) as e:
+        S.find_poseidon_ark_and_mds("bn254", 255, 2, 8, 57, 0)   # assert_eq!(MODULUS_BIT_SIZE, prime_num_bits)
+    assert e.value.status == 2
+    d = S.get_default_poseidon_parameters("bn254", 2, False)
+    assert (d.full_rounds, d.partial_rounds, d.alpha) == (8, 57, 5) and d.ark == oracle_cfg(ref, "bn254_t3").ark
+
+
+def test_config_shape_asserts(S):
+    """PoseidonConfig::new asserts, mod.rs:196-203."""
+    ok = dict(full_rounds=2, partial_rounds=1, alpha=5, mds=[[1, 2], [3, 4]], ark=[[1, 2]] * 3, rate=1, capacity=1)
+    S.PoseidonConfig(**ok)
+    for bad in (dict(ok, ark=[[1, 2]] * 2), dict(ok, ark=[[1]] * 3), dict(ok, mds=[[1, 2]]), dict(ok, mds=[[1], [2]])):
+        with pytest.raises(AssertionError):
+            S.PoseidonConfig(**bad)
+    assert S.PoseidonParameters is S.PoseidonConfig
+
+
+def test_product_fails_loudly_without_gpu(S, ref):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    cfg = S.get_default_poseidon_parameters("bls12_381", 2, False)
+    with pytest.raises(S.PoseidonB200Error) as e:
+        S.PoseidonSponge.new(cfg)
+    assert e.value.status == 4 and "no CPU path" in str(e.value)
+
+
+def test_c_abi_argument_errors(S):
+    from sponge_b200 import _lib as L
+    lib = L.lib
+    h = C.c_void_p()
+    assert lib.psd_ctx_create(None, 0, C.byref(h)) == L.PSD_ERR_ARG
+    ark = np.zeros((3 * 3, 4), dtype=np.uint64)
+    mds = np.zeros((9, 4), dtype=np.uint64)
+    p = L.PsdParams(7, 2, 1, 5, 2, 1, ark.ctypes.data, mds.ctypes.data, 0)
+    assert lib.psd_ctx_create(C.byref(p), 0, C.byref(h)) == L.PSD_ERR_ARG            # unknown field
+    p = L.PsdParams(0, 2, 1, 5, 2, 1, None, mds.ctypes.data, 0)
+    assert lib.psd_ctx_create(C.byref(p), 0, C.byref(h)) == L.PSD_ERR_SHAPE          # ark missing
+    p = L.PsdParams(0, 2, 1, 5, 12, 1, ark.ctypes.data, mds.ctypes.data, 0)
+    assert lib.psd_ctx_create(C.byref(p), 0, C.byref(h)) == L.PSD_ERR_UNSUPPORTED    # t = 13
+    p = L.PsdParams(0, 2, 1, 5, 0, 3, ark.ctypes.data, mds.ctypes.data, 0)
+    assert lib.psd_ctx_create(C.byref(p), 0, C.byref(h)) == L.PSD_ERR_SHAPE          # rate 0
+    assert lib.psd_permute_batch(None, ark.ctypes.data, 1, 0, 1, 0, None) == L.PSD_ERR_ARG
+    assert lib.psd_batch_new(None, 1, C.byref(h)) == L.PSD_ERR_ARG
+    assert lib.psd_sponge_new(None, C.byref(h)) == L.PSD_ERR_ARG
+    assert b"null" in lib.psd_last_error_string()
+    lib.psd_ctx_destroy(None)
+    lib.psd_batch_free(None)
+    lib.psd_sponge_free(None)
+    assert lib.psd_batch_size(None) == 0
+
+
+def test_limb_helpers_and_enums(S):
+    vals = [0, 1, (1 << 255) - 19, S.MODULUS["bn254"] - 1]
+    assert S.limbs_to_ints(S.ints_to_limbs(vals)) == vals
+    assert S.ints_to_limbs([1 + (2 << 64)]).tolist() == [[1, 2, 0, 0]]
+    assert S.FieldElementSize.Truncated(100).num_bits("bls12_381") == 254     # quirk Q3, lib.rs:45-52
+    assert S.FieldElementSize.Full().num_bits("bn254") == 253
+    with pytest.raises(ValueError):
+        S.FieldElementSize.Truncated(256).num_bits("bls12_381")
+    assert S.DuplexSpongeMode.Absorbing(0) != S.DuplexSpongeMode.Squeezing(0)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    so = os.path.join(ROOT, "tests", "emu", "libfp_emu.so")
+    csrc = os.path.join(ROOT, "sponge_b200", "csrc")
+    srcs = [os.path.join(ROOT, "tests", "emu", "fp_emu.cpp"), os.path.join(csrc, "opt_constants.cpp"),
+            os.path.join(csrc, "params.cpp")]
+    deps = srcs + [os.path.join(csrc, h) for h in ("fp256.cuh", "poseidon_core.cuh", "opt_constants.hpp",
+                                                   "host_field.hpp", "params.hpp")]
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", so] + srcs)
+    return C.CDLL(so)
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_device_arithmetic_host_model(emu, ref, field):
+    """sponge_b200/csrc/fp256.cuh compiled for the host (C model of each PTX carry chain):
+    Montgomery product, modular add and the pow ladder are exact, including edge operands."""
+    p = ref.BN254_FR if field == 0 else ref.BLS12_381_FR
+    rng = random.Random(field)
+    n = 4000
+    A = [rng.randrange(p) for _ in range(n)]
+    B = [rng.randrange(p) for _ in range(n)]
+    A[:8] = [0, p - 1, p - 1, 1, 0, p - 2, (1 << 253) - 1, 1 << 253]
+    B[:8] = [0, p - 1, 1, p - 1, p - 1, p - 1, p - 1, (1 << 253) + 5]
+    a, b = to_limbs(A).view(np.uint32), to_limbs(B).view(np.uint32)
+    r = np.zeros_like(a)
+    rinv = pow(1 << 256, -1, p)
+    emu.emu_mont_mul(field, r.ctypes.data, a.ctypes.data, b.ctypes.data, C.c_size_t(n))
+    assert to_ints(r.view(np.uint64)) == [x * y * rinv % p for x, y in zip(A, B)]
+    emu.emu_add(field, r.ctypes.data, a.ctypes.data, b.ctypes.data, C.c_size_t(n))
+    assert to_ints(r.view(np.uint64)) == [(x + y) % p for x, y in zip(A, B)]
+    one = to_limbs([(1 << 256) % p]).view(np.uint32)
+    for alpha in (5, 17, 257, 3, 1, 0):
+        emu.emu_pow(field, r.ctypes.data, a.ctypes.data, C.c_uint64(alpha), one.ctypes.data, C.c_size_t(400))
+        exp = [pow(x * rinv % p, alpha, p) * (1 << 256) % p for x in A[:400]]
+        assert to_ints(r.view(np.uint64))[:400] == exp
+
+
+@pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bls_default_r2", "bls_fixture", "bn254_t2",
+                                  "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r2_w"])
+def test_permutation_variants_host_model(emu, ref, name):
+    """The device permutation code (poseidon_core.cuh: dense, optimised sparse/lazy form, rolled form)
+    compiled for the host with the product's own constant derivation (opt_constants.cpp), against the
+    oracle.  This checks the algebra of the optimised form without a GPU; the PTX mapping itself is
+    covered by the -m gpu tests."""
+    from conftest import field_id
+    from oracle.c_oracle import COracle
+    cfg = oracle_cfg(ref, name)
+    fid = field_id(ref, cfg)
+    t = cfg.rate + cfg.capacity
+    orc = COracle(cfg, fid)
+    n = 24
+    st = orc.synth(n * t, seed=5)
+    st[:t] = 0
+    exp = orc.permute_batch(st.copy())
+    ark = to_limbs(v for r in cfg.ark for v in r)
+    mds = to_limbs(v for r in cfg.mds for v in r)
+    for variant in (0, 1, 2):
+        s = st.copy().view(np.uint32)
+        rc = emu.emu_permute(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
+                             C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), variant,
+                             C.c_void_p(s.ctypes.data), C.c_size_t(n))
+        assert rc == 0, (variant, rc)
+        assert np.array_equal(s.view(np.uint64), exp), f"variant {variant} differs from the oracle"
+
+
+def test_mont_dot_host_model(emu, ref):
+    """Lazily reduced dot product (one Montgomery reduction for N products), BN254, worst-case operands."""
+    p = ref.BN254_FR
+    rng = random.Random(4)
+    rinv = pow(1 << 256, -1, p)
+    for n_terms in (1, 2, 3, 4):
+        n = 1500
+        A = [[rng.randrange(p) for _ in range(n_terms)] for _ in range(n)]
+        B = [[rng.randrange(p) for _ in range(n_terms)] for _ in range(n)]
+        A[0] = [p - 1] * n_terms
+        B[0] = [p - 1] * n_terms
+        A[1] = [0] * n_terms
+        a = to_limbs(v for r in A for v in r).view(np.uint32)
+        b = to_limbs(v for r in B for v in r).view(np.uint32)
+        r = np.zeros(n * 8, dtype=np.uint32)
+        emu.emu_mont_dot(n_terms, C.c_void_p(r.ctypes.data), C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data),
+                         C.c_size_t(n))
+        assert to_ints(r.view(np.uint64)) == [sum(x * y for x, y in zip(ra, rb)) * rinv % p for ra, rb in zip(A, B)]
