@@ -64,21 +64,26 @@ __global__ void __launch_bounds__(256) synth_kernel(PermDesc d, uint32_t* elems,
 }
 
 // ------------------------------------------------------------------------------------------------
-// K0: integer-multiply throughput probes.  Every thread runs 8 independent chains so the multiplier
-// pipe, not latency, is the limit; the result is stored so nothing is optimised away.
+// K0: integer-multiply throughput probes.  Every thread runs 8 independent chains and every
+// multiply takes one operand from its own running accumulator, so ptxas can neither hoist the
+// product out of the loop nor strength-reduce it into adds (a first version with loop-invariant
+// operands was silently turned into IADD3 chains).  Results are stored conditionally so nothing is
+// optimised away.
+//   kind 0: IMAD.WIDE.U32 (32x32+64 -> 64)     kind 1: IMAD (32x32+32 -> low 32)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) imad_wide_kernel(uint32_t* scratch, uint32_t iters) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t a = scratch[tid & 1023] | 1u, b = scratch[(tid + 7) & 1023] | 3u;
+    const uint32_t b = scratch[(tid + 7) & 1023] | 3u;
     uint64_t acc[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) acc[k] = tid + k;
+    for (int k = 0; k < 8; k++) acc[k] = scratch[(tid + k) & 1023] + k;
 #pragma unroll 1
     for (uint32_t it = 0; it < iters; it++) {
 #pragma unroll
         for (int rep = 0; rep < 8; rep++) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(a), "r"(b));
+            for (int k = 0; k < 8; k++)
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"((uint32_t)acc[k]), "r"(b));
         }
     }
     uint64_t s = 0;
@@ -89,16 +94,16 @@ __global__ void __launch_bounds__(256) imad_wide_kernel(uint32_t* scratch, uint3
 
 __global__ void __launch_bounds__(256) imad_lo_kernel(uint32_t* scratch, uint32_t iters) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t a = scratch[tid & 1023] | 1u, b = scratch[(tid + 7) & 1023] | 3u;
+    const uint32_t b = scratch[(tid + 7) & 1023] | 3u;
     uint32_t acc[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) acc[k] = tid + k;
+    for (int k = 0; k < 8; k++) acc[k] = scratch[(tid + k) & 1023] + k;
 #pragma unroll 1
     for (uint32_t it = 0; it < iters; it++) {
 #pragma unroll
         for (int rep = 0; rep < 8; rep++) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(acc[k]) : "r"(a), "r"(b));
+            for (int k = 0; k < 8; k++) asm volatile("mad.lo.u32 %0, %0, %1, %0;" : "+r"(acc[k]) : "r"(b));
         }
     }
     uint32_t s = 0;
