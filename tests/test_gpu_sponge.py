@@ -227,3 +227,13 @@ def test_sponge_batch_lockstep(S, ref):
         assert np.array_equal(b2.squeeze_native(2), b.squeeze_native(2))
     finally:
         ctx.close()
+
+
+def test_cpp_wrapper_reference_kat(S):
+    """The C++ mirror (include/poseidon_b200.hpp) reproduces src/poseidon/mod.rs:376-399 on the GPU."""
+    import subprocess
+    from test_host_logic import _build_cpp_wrapper_test
+    exe = _build_cpp_wrapper_test(S)
+    kat = load_golden("reference_kats.json")["sponge_consistency"]["squeeze_native"]
+    r = subprocess.run([exe] + ["%064x" % int(v) for v in kat], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr

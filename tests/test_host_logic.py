@@ -207,3 +207,27 @@ def test_mont_dot_host_model(emu, ref):
         emu.emu_mont_dot(n_terms, C.c_void_p(r.ctypes.data), C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data),
                          C.c_size_t(n))
         assert to_ints(r.view(np.uint64)) == [sum(x * y for x, y in zip(ra, rb)) * rinv % p for ra, rb in zip(A, B)]
+
+
+def _build_cpp_wrapper_test(S):
+    exe = os.path.join(ROOT, "tests", "cpp", "wrapper_test")
+    src = exe + ".cpp"
+    hdrs = [os.path.join(ROOT, "include", h) for h in ("poseidon_b200.hpp", "poseidon_b200.h")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(p) for p in [src, S.LIB_PATH] + hdrs):
+        libdir = os.path.dirname(S.LIB_PATH)
+        subprocess.check_call(["g++", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", exe, src,
+                               "-L" + libdir, "-lposeidon_b200", "-Wl,-rpath," + libdir])
+    return exe
+
+
+def test_cpp_wrapper_compiles_and_refuses_without_gpu(S):
+    """include/poseidon_b200.hpp builds against the C ABI; without a GPU the program reports PSD_ERR_CUDA
+    (exit code 3) instead of computing anything on the CPU."""
+    import torch
+    exe = _build_cpp_wrapper_test(S)
+    kat = load_golden("reference_kats.json")["sponge_consistency"]["squeeze_native"]
+    r = subprocess.run([exe] + ["%064x" % int(v) for v in kat], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert r.returncode == 0, r.stdout
+    else:
+        assert r.returncode == 3 and "no CPU path" in r.stdout
