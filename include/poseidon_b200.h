@@ -143,6 +143,33 @@ psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves
 psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, uint64_t* out, int repr,
                               int mem, void* stream);
 
+/* Merkle root for callers that must not allocate.  No counterpart in the reference (like
+ * psd_merkle_root it is defined through the reference sponge; this variant exists only because of
+ * how some hosts manage GPU memory).
+ *
+ * Who needs it: a proving service that carves up its whole device-memory budget at start-up and
+ * hands every byte to its own arena cannot let a library call cudaMalloc afterwards -- the call can
+ * fail outright (nothing is left outside the arena), it takes a process-wide driver lock that stalls
+ * the other streams, and in such code bases an allocation on the request path is treated as a bug.
+ * psd_merkle_root allocates and frees its level buffers on every call, so it is unusable there.
+ *
+ * This entry point computes the same root with the intermediate levels kept in a fixed scratch
+ * array that is part of the library image: PSD_NOALLOC_MAX_LEAVES/2 + PSD_NOALLOC_MAX_LEAVES/4
+ * elements = 1.5 MiB, resident on every GPU that loads the library until the process exits.  It
+ * calls no cudaMalloc/cudaFree and no allocating library routine.  `leaves` (n_leaves elements,
+ * AoS) and `root` (1 element) are DEVICE pointers on the context's device; the work is queued on
+ * `stream` and the call returns without waiting (a non-canonical leaf is reported by the next
+ * psd_stream_synchronize, as for the other device-pointer calls).
+ *   - n_leaves must be a power of two and <= PSD_NOALLOC_MAX_LEAVES, else PSD_ERR_ARG.
+ *   - The first call on a device looks up the scratch array's device address (once per device, with
+ *     that device current); make that first call before any stream capture begins.
+ *   - All calls share the one array and it keeps whatever the last call left in it.  Nothing has
+ *     to be cleared: each level is written in full before the next level reads it.  Two calls that
+ *     overlap on the GPU (different streams, or threads) race on it -- serialise them. */
+#define PSD_NOALLOC_MAX_LEAVES 65536
+psd_status psd_merkle_root_noalloc(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root, int repr,
+                                   void* stream);
+
 /* ---- lock-step batch of sponges (absorb/squeeze bookkeeping lifted to batch) --------------------
  * A psd_batch is n PoseidonSponge<F> values that always receive calls of identical shape, so they
  * share one DuplexSpongeMode; states stay in HBM between calls (SoA, Montgomery). */

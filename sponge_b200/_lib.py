@@ -67,6 +67,7 @@ _PROTOS = {
     "psd_absorb_squeeze_bytes_batch": (_i, [_vp, _vp, _sz, _u32, _u32, _vp, _i, _i, _i, _vp]),
     "psd_merkle_root": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
     "psd_compress_pairs": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
+    "psd_merkle_root_noalloc": (_i, [_vp, _vp, _sz, _vp, _i, _vp]),
     "psd_batch_new": (_i, [_vp, _sz, _pp]),
     "psd_batch_clone": (_i, [_vp, _pp]),
     "psd_batch_free": (None, [_vp]),

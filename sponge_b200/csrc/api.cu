@@ -1320,3 +1320,89 @@ psd_status psd_sponge_set_state(psd_sponge* s, const uint64_t* state, int repr, 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Merkle root without any allocation (see include/poseidon_b200.h).  The level buffers live in a
+// fixed array inside the library image instead of a cudaMalloc'd block: hosts that give all device
+// memory to their own arena at start-up cannot tolerate a cudaMalloc on the request path.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kNoAllocLevel1 = PSD_NOALLOC_MAX_LEAVES / 2;   // elements in the first level
+constexpr size_t kNoAllocLevel2 = PSD_NOALLOC_MAX_LEAVES / 4;   // elements in the second level
+// 8 words per element; 1.5 MiB on every GPU that loads the library, for the life of the process.
+static __device__ __align__(256) uint32_t g_noalloc_scratch[(kNoAllocLevel1 + kNoAllocLevel2) * 8];
+
+// In host code the name g_noalloc_scratch is only a handle for the symbol, not an address the GPU
+// can use; the real device address is looked up once per device and cached here.
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_ptr[64] = {nullptr};
+
+// Requires the target device to be current.
+psd_status noalloc_scratch_for(int device, uint32_t** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(PSD_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d failed: %s", device,
+                        cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[device] = static_cast<uint32_t*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return PSD_OK;
+}
+
+}  // namespace
+
+extern "C" psd_status psd_merkle_root_noalloc(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root,
+                                              int repr, void* stream) {
+    if (!ctx) return fail(PSD_ERR_ARG, "null context");
+    if (!leaves || !root) return fail(PSD_ERR_ARG, "null buffer");
+    if (!valid_enum(repr, 1)) return fail(PSD_ERR_ARG, "bad repr value");
+    if (ctx->rate < 2) return fail(PSD_ERR_UNSUPPORTED, "2-to-1 compression needs rate >= 2");
+    if (n_leaves == 0 || (n_leaves & (n_leaves - 1))) return fail(PSD_ERR_ARG, "n_leaves must be a power of two");
+    if (n_leaves > PSD_NOALLOC_MAX_LEAVES)
+        return fail(PSD_ERR_ARG,
+                    "psd_merkle_root_noalloc: n_leaves = %zu exceeds PSD_NOALLOC_MAX_LEAVES = %d (the fixed scratch "
+                    "array holds no more); use psd_merkle_root or split the tree",
+                    n_leaves, PSD_NOALLOC_MAX_LEAVES);
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", ctx->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_leaves == 1) {
+        PSD_CUDA(cudaMemcpyAsync(root, leaves, 32, cudaMemcpyDeviceToDevice, s));
+        return PSD_OK;
+    }
+    uint32_t* scratch = nullptr;
+    psd_status st = noalloc_scratch_for(ctx->device, &scratch);
+    if (st != PSD_OK) return st;
+    // Levels alternate between the two halves of the scratch array; the last level (one pair) is
+    // written straight to the caller's root.  Every element a level reads was written by the level
+    // before it in this same call, so stale contents from earlier calls are never observed.
+    uint32_t* bufs[2] = {scratch, scratch + kNoAllocLevel1 * 8};
+    const uint32_t* src = as_u32(leaves);
+    int src_repr = repr;
+    int which = 0;
+    for (size_t pairs = n_leaves / 2; pairs >= 1; pairs /= 2) {
+        SpongeArgs a = base_args(ctx, pairs);
+        a.in = src;
+        a.n_absorb = 2;
+        a.in_layout = kLayoutAos;
+        a.in_repr = src_repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = 1;
+        a.out = pairs == 1 ? as_u32(root) : bufs[which];
+        a.out_layout = kLayoutAos;
+        a.out_repr = pairs == 1 ? repr : kReprMontgomery;
+        st = launch(ctx, a, s);
+        if (st != PSD_OK) return st;
+        src = bufs[which];
+        src_repr = kReprMontgomery;
+        which ^= 1;
+        if (pairs == 1) break;
+    }
+    return PSD_OK;
+}
