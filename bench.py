@@ -293,6 +293,7 @@ def main():
 
         def step():
             b = S.SpongeBatch(ctx, n)
+            b.set_stream(sptr)
             for _ in range(1024 // chunk):
                 b.absorb_dev(buf.data_ptr(), chunk)
             b.squeeze_bytes_dev(32, outb.data_ptr())

@@ -191,6 +191,9 @@ psd_status psd_batch_get_state(const psd_batch* b, uint64_t* states, int layout,
 psd_status psd_batch_set_state(psd_batch* b, const uint64_t* states, int layout, int repr, int mem,
                                int mode, uint32_t index);
 size_t psd_batch_size(const psd_batch* b);
+/* Run this batch's kernels and copies on the caller's stream (NULL = back to the batch's own
+ * stream).  Calls still return only when their work is complete. */
+psd_status psd_batch_set_stream(psd_batch* b, void* stream);
 
 /* ---- single-sponge drop-in (CryptographicSponge, lib.rs:105-158; FieldBasedCryptographicSponge,
  * lib.rs:162-183).  A batch of one: latency-bound, exists for API parity. Host pointers. ---------- */

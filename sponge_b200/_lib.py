@@ -77,6 +77,7 @@ _PROTOS = {
     "psd_batch_get_state": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(_i), C.POINTER(_u32)]),
     "psd_batch_set_state": (_i, [_vp, _vp, _i, _i, _i, _i, _u32]),
     "psd_batch_size": (_sz, [_vp]),
+    "psd_batch_set_stream": (_i, [_vp, _vp]),
     "psd_sponge_new": (_i, [_vp, _pp]),
     "psd_sponge_clone": (_i, [_vp, _pp]),
     "psd_sponge_free": (None, [_vp]),

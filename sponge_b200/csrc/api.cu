@@ -928,7 +928,8 @@ struct psd_batch {
     uint32_t* d_state = nullptr;   // SoA, Montgomery, n * t elements
     int mode = kModeAbsorbing;
     uint32_t index = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // stream in use (own_stream unless the caller set one)
+    cudaStream_t own_stream = nullptr;
     void* d_io = nullptr;          // device staging for host-side inputs/outputs
     size_t d_io_bytes = 0;
 };
@@ -980,7 +981,8 @@ psd_status psd_batch_new(psd_ctx* ctx, size_t n, psd_batch** out) {
         delete b;
         return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for batch state failed", bytes);
     }
-    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        (b->stream = b->own_stream, false) ||
         cudaMemsetAsync(b->d_state, 0, bytes, b->stream) != cudaSuccess ||   // vec![F::zero(); t], mod.rs:220
         cudaStreamSynchronize(b->stream) != cudaSuccess) {
         psd_status st = fail(PSD_ERR_CUDA, "batch init failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -1014,10 +1016,8 @@ void psd_batch_free(psd_batch* b) {
     if (!b) return;
     {
         DeviceGuard guard(b->ctx->device);
-        if (b->stream) {
-            cudaStreamSynchronize(b->stream);
-            cudaStreamDestroy(b->stream);
-        }
+        if (b->stream) cudaStreamSynchronize(b->stream);
+        if (b->own_stream) cudaStreamDestroy(b->own_stream);
         if (b->d_state) cudaFree(b->d_state);
         if (b->d_io) cudaFree(b->d_io);
     }
@@ -1026,6 +1026,14 @@ void psd_batch_free(psd_batch* b) {
 }
 
 size_t psd_batch_size(const psd_batch* b) { return b ? b->n : 0; }
+
+psd_status psd_batch_set_stream(psd_batch* b, void* stream) {
+    if (!b) return fail(PSD_ERR_ARG, "null batch");
+    DeviceGuard guard(b->ctx->device);
+    PSD_CUDA(cudaStreamSynchronize(b->stream));
+    b->stream = stream ? (cudaStream_t)stream : b->own_stream;
+    return PSD_OK;
+}
 
 psd_status psd_batch_absorb(psd_batch* b, const uint64_t* elems, uint32_t k, int layout, int repr, int mem) {
     if (!b) return fail(PSD_ERR_ARG, "null batch");

@@ -301,6 +301,9 @@ class SpongeBatch:
     def free(self) -> None:
         self._fin()
 
+    def set_stream(self, stream: int) -> None:
+        check(lib.psd_batch_set_stream(self.handle, stream or None))
+
     def absorb(self, elems: np.ndarray, k: int, layout=L.LAYOUT_AOS, repr=L.REPR_MONTGOMERY) -> None:
         assert elems.dtype == np.uint64 and elems.flags.c_contiguous and elems.size == self.n * k * 4
         check(lib.psd_batch_absorb(self.handle, _ptr(elems), k, layout, repr, L.MEM_HOST))
