@@ -107,11 +107,22 @@ def units_and_perms(name, w, n):
 # ------------------------------------------------------------------------------------------------
 # CPU baseline: the C port of the reference's CPU path on the host cores (bounded sample)
 # ------------------------------------------------------------------------------------------------
+def host_threads():
+    """All host threads this process may use.  Passed explicitly to the OpenMP oracle because torchrun
+    exports OMP_NUM_THREADS=1 to its workers."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(name, w, seconds, threads=0):
     from oracle.c_oracle import COracle
     ocfg, fid = oracle_config(w)
     orc = COracle(ocfg, fid)
-    cores = orc.max_threads() if threads <= 0 else threads
+    if threads <= 0:
+        threads = host_threads()
+    cores = threads
     t = w["rate"] + 1
 
     def run(n):
@@ -142,7 +153,7 @@ def cpu_baseline(name, w, seconds, threads=0):
     while n * 2 * (512 if name == "c5" else 1) / rate <= seconds and n < (1 << 22):
         n *= 2
     dt, units = run(n)
-    return dict(value=units / dt, unit="perm/s", cores=cores, kind="port",
+    return dict(value=units / dt, unit="perm/s", cores=cores, kind="port", seconds=dt,
                 sample=f"{n} {'sponges x 512 perms' if name == 'c5' else 'units'} of workload {name} "
                        f"({dt:.1f} s, OpenMP over independent sponges)")
 
@@ -212,17 +223,19 @@ def main():
         if rank != 0:
             return
         best = None
-        vals = []
+        vals, secs = [], []
         per_step = max(2.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
         for i in range(args.warmup + args.steps):
             r = cpu_baseline(name, w, per_step)
             if i >= args.warmup:
                 vals.append(r["value"])
+                secs.append(r["seconds"])
                 best = r
         value = sum(vals) / len(vals)
         best["value"] = value
         line = dict(impl="reference", metric="poseidon_permutations_per_second", value=value, unit="perm/s",
-                    n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=None, higher_is_better=True,
+                    n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * sum(secs) / len(secs),
+                    higher_is_better=True,
                     scaling="weak", vs_baseline=None, dtype="u32x8 (256-bit Montgomery, 4x64-bit limbs on CPU)",
                     data="synthetic", config=dict(workload=f"{name}: {w['desc']}", sample=best["sample"]),
                     cpu_baseline=best,
