@@ -41,6 +41,7 @@ struct Bn254Fr {
     static constexpr uint32_t P0 = 0xf0000001u, P1 = 0x43e1f593u, P2 = 0x79b97091u, P3 = 0x2833e848u,
                               P4 = 0x8181585du, P5 = 0xb85045b6u, P6 = 0xe131a029u, P7 = 0x30644e72u;
     static constexpr uint32_t NP0 = 0xefffffffu;
+    static constexpr bool kModulusFromConstBank = false;
 };
 struct Bls12381Fr {
     static constexpr int kFieldId = 1;
@@ -48,7 +49,34 @@ struct Bls12381Fr {
     static constexpr uint32_t P0 = 0x00000001u, P1 = 0xffffffffu, P2 = 0xfffe5bfeu, P3 = 0x53bda402u,
                               P4 = 0x09a1d805u, P5 = 0x3339d808u, P6 = 0x299d7d48u, P7 = 0x73eda753u;
     static constexpr uint32_t NP0 = 0xffffffffu;
+    // With p0 = 1 and p1 = 2^32-1 as immediates ptxas rewrites m*p into IMAD.X / IMAD.HI.U32.X pairs
+    // (6 multiplier-pipe cycles per product instead of 4); reading the limbs from the constant bank
+    // keeps them opaque, so every product stays one IMAD.WIDE.U32.X with a uniform-register operand.
+    static constexpr bool kModulusFromConstBank = true;
 };
+
+#if defined(__CUDACC__)
+__constant__ uint32_t c_bls12_381_fr_p[9] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u,
+                                             0x09a1d805u, 0x3339d808u, 0x299d7d48u, 0x73eda753u, 0xffffffffu};
+#else
+static const uint32_t c_bls12_381_fr_p[9] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u,
+                                             0x09a1d805u, 0x3339d808u, 0x299d7d48u, 0x73eda753u, 0xffffffffu};
+#endif
+
+// -p^-1 mod 2^32 as the multiplier sees it
+template <class F>
+PSD_DEV uint32_t np0() {
+    if (F::kModulusFromConstBank) return c_bls12_381_fr_p[8];
+    return F::NP0;
+}
+
+// k-th modulus limb as the multiplier sees it (immediate or constant-bank operand)
+template <class F, int K>
+PSD_DEV uint32_t plimb() {
+    if (F::kModulusFromConstBank) return c_bls12_381_fr_p[K];
+    return K == 0 ? F::P0 : K == 1 ? F::P1 : K == 2 ? F::P2 : K == 3 ? F::P3 : K == 4 ? F::P4 : K == 5 ? F::P5
+         : K == 6 ? F::P6 : F::P7;
+}
 
 // ------------------------------------------------------------------------------------------------
 // Carry-chain primitives.  An accumulator is uint32_t[8] holding four (lo,hi) pairs.
@@ -166,6 +194,121 @@ PSD_DEV void mad4_slide(uint32_t* x, uint32_t& y0, uint32_t a0, uint32_t a1, uin
 #endif
 }
 
+// ---- partial chains for squaring: products for the first S pairs are omitted -------------------
+// d pairs S..3 += {a_S..a_3} * b, carry out of the top pair added to `top`.  S == 4: nothing to do.
+template <int S>
+PSD_DEV void mad4_from(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b,
+                       uint32_t& top) {
+    if (S <= 0) {
+        mad4(d, a0, a1, a2, a3, b, top);
+        return;
+    }
+    if (S >= 4) return;
+#if !defined(PSD_HOST_EMU)
+    if (S == 1) {
+        asm("mad.lo.cc.u32 %0, %7, %10, %0;\n\t"
+            "madc.hi.cc.u32 %1, %7, %10, %1;\n\t"
+            "madc.lo.cc.u32 %2, %8, %10, %2;\n\t"
+            "madc.hi.cc.u32 %3, %8, %10, %3;\n\t"
+            "madc.lo.cc.u32 %4, %9, %10, %4;\n\t"
+            "madc.hi.cc.u32 %5, %9, %10, %5;\n\t"
+            "addc.u32 %6, %6, 0;"
+            : "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7]), "+r"(top)
+            : "r"(a1), "r"(a2), "r"(a3), "r"(b));
+    } else if (S == 2) {
+        asm("mad.lo.cc.u32 %0, %5, %7, %0;\n\t"
+            "madc.hi.cc.u32 %1, %5, %7, %1;\n\t"
+            "madc.lo.cc.u32 %2, %6, %7, %2;\n\t"
+            "madc.hi.cc.u32 %3, %6, %7, %3;\n\t"
+            "addc.u32 %4, %4, 0;"
+            : "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7]), "+r"(top)
+            : "r"(a2), "r"(a3), "r"(b));
+    } else {
+        asm("mad.lo.cc.u32 %0, %3, %4, %0;\n\t"
+            "madc.hi.cc.u32 %1, %3, %4, %1;\n\t"
+            "addc.u32 %2, %2, 0;"
+            : "+r"(d[6]), "+r"(d[7]), "+r"(top)
+            : "r"(a3), "r"(b));
+    }
+#else
+    const uint32_t a[4] = {a0, a1, a2, a3};
+    uint64_t c = 0;
+    for (int k = S; k < 4; k++) {
+        unsigned __int128 w = (unsigned __int128)((uint64_t)a[k] * b) +
+                              (((uint64_t)d[2 * k + 1] << 32) | d[2 * k]) + c;
+        d[2 * k] = (uint32_t)w;
+        d[2 * k + 1] = (uint32_t)(w >> 32);
+        c = (uint64_t)(w >> 64);
+    }
+    top += (uint32_t)c;
+#endif
+}
+
+// mad4_slide with the products of the first S pairs omitted (those pairs are only shifted down and
+// take the carry).  S in 0..3.
+template <int S>
+PSD_DEV void mad4_slide_from(uint32_t* x, uint32_t& y0, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                             uint32_t b) {
+    if (S <= 0) {
+        mad4_slide(x, y0, a0, a1, a2, a3, b);
+        return;
+    }
+#if !defined(PSD_HOST_EMU)
+    if (S == 1) {
+        asm("add.cc.u32 %8, %8, %1;\n\t"
+            "addc.cc.u32 %0, %2, 0;\n\t"
+            "addc.cc.u32 %1, %3, 0;\n\t"
+            "madc.lo.cc.u32 %2, %9, %12, %4;\n\t"
+            "madc.hi.cc.u32 %3, %9, %12, %5;\n\t"
+            "madc.lo.cc.u32 %4, %10, %12, %6;\n\t"
+            "madc.hi.cc.u32 %5, %10, %12, %7;\n\t"
+            "madc.lo.cc.u32 %6, %11, %12, 0;\n\t"
+            "madc.hi.u32 %7, %11, %12, 0;"
+            : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]),
+              "+r"(y0)
+            : "r"(a1), "r"(a2), "r"(a3), "r"(b));
+    } else if (S == 2) {
+        asm("add.cc.u32 %8, %8, %1;\n\t"
+            "addc.cc.u32 %0, %2, 0;\n\t"
+            "addc.cc.u32 %1, %3, 0;\n\t"
+            "addc.cc.u32 %2, %4, 0;\n\t"
+            "addc.cc.u32 %3, %5, 0;\n\t"
+            "madc.lo.cc.u32 %4, %9, %11, %6;\n\t"
+            "madc.hi.cc.u32 %5, %9, %11, %7;\n\t"
+            "madc.lo.cc.u32 %6, %10, %11, 0;\n\t"
+            "madc.hi.u32 %7, %10, %11, 0;"
+            : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]),
+              "+r"(y0)
+            : "r"(a2), "r"(a3), "r"(b));
+    } else {
+        asm("add.cc.u32 %8, %8, %1;\n\t"
+            "addc.cc.u32 %0, %2, 0;\n\t"
+            "addc.cc.u32 %1, %3, 0;\n\t"
+            "addc.cc.u32 %2, %4, 0;\n\t"
+            "addc.cc.u32 %3, %5, 0;\n\t"
+            "addc.cc.u32 %4, %6, 0;\n\t"
+            "addc.cc.u32 %5, %7, 0;\n\t"
+            "madc.lo.cc.u32 %6, %9, %10, 0;\n\t"
+            "madc.hi.u32 %7, %9, %10, 0;"
+            : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]),
+              "+r"(y0)
+            : "r"(a3), "r"(b));
+    }
+#else
+    const uint32_t a[4] = {a0, a1, a2, a3};
+    uint64_t s = (uint64_t)y0 + x[1];
+    y0 = (uint32_t)s;
+    uint64_t c = s >> 32;
+    for (int k = 0; k < 4; k++) {
+        uint64_t add = (k < 3) ? ((((uint64_t)x[2 * k + 3]) << 32) | x[2 * k + 2]) : 0;
+        unsigned __int128 w = (unsigned __int128)(k >= S ? (uint64_t)a[k] * b : 0) + add + c;
+        x[2 * k] = (uint32_t)w;
+        x[2 * k + 1] = (uint32_t)(w >> 32);
+        c = (uint64_t)(w >> 64);
+    }
+#endif
+}
+
 // r = w + (z >> 32), z[0] == 0: merges the two accumulators after the last row.
 PSD_DEV void merge8(uint32_t* r, const uint32_t* w, const uint32_t* z) {
 #if !defined(PSD_HOST_EMU)
@@ -266,9 +409,9 @@ template <class F>
 PSD_DEV void mont_row(uint32_t* x, uint32_t* y, const uint32_t* a, uint32_t bi) {
     mad4_slide(x, y[0], a[1], a[3], a[5], a[7], bi);
     mad4(y, a[0], a[2], a[4], a[6], bi, x[7]);
-    const uint32_t m = y[0] * F::NP0;
-    mad4_nc(x, F::P1, F::P3, F::P5, F::P7, m);
-    mad4(y, F::P0, F::P2, F::P4, F::P6, m, x[7]);
+    const uint32_t m = y[0] * np0<F>();
+    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
 }
 
 // r = a * b * 2^-256 mod p, fully reduced.  Requires a < 2^255 (true for any residue of either
@@ -281,9 +424,9 @@ PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     uint32_t e[8], o[8];
     mul4(e, a[0], a[2], a[4], a[6], b[0]);
     mul4(o, a[1], a[3], a[5], a[7], b[0]);
-    const uint32_t m = e[0] * F::NP0;
-    mad4_nc(o, F::P1, F::P3, F::P5, F::P7, m);
-    mad4(e, F::P0, F::P2, F::P4, F::P6, m, o[7]);
+    const uint32_t m = e[0] * np0<F>();
+    mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
     mont_row<F>(e, o, a, b[1]);
     mont_row<F>(o, e, a, b[2]);
     mont_row<F>(e, o, a, b[3]);
@@ -314,9 +457,9 @@ PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8
         mad4(e, a[j][0], a[j][2], a[j][4], a[j][6], b[j][0], o[7]);
     }
     {
-        const uint32_t m = e[0] * F::NP0;
-        mad4_nc(o, F::P1, F::P3, F::P5, F::P7, m);
-        mad4(e, F::P0, F::P2, F::P4, F::P6, m, o[7]);
+        const uint32_t m = e[0] * np0<F>();
+        mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+        mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
     }
     // rows 1..7: x = accumulator whose column 0 is now zero, y = the other one
 #pragma unroll
@@ -330,9 +473,9 @@ PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8
             mad4_nc(x, a[j][1], a[j][3], a[j][5], a[j][7], b[j][i]);
             mad4(y, a[j][0], a[j][2], a[j][4], a[j][6], b[j][i], x[7]);
         }
-        const uint32_t m = y[0] * F::NP0;
-        mad4_nc(x, F::P1, F::P3, F::P5, F::P7, m);
-        mad4(y, F::P0, F::P2, F::P4, F::P6, m, x[7]);
+        const uint32_t m = y[0] * np0<F>();
+        mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+        mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
     }
     uint32_t s[8];
     merge8(s, e, o);        // after row 7: o[0] == 0
@@ -345,13 +488,77 @@ struct DotLimit {
     static constexpr int kMax = (F::kBits == 254) ? 4 : 1;
 };
 
+// One CIOS row of the squaring: only the products a_i * v_j with j >= i are added
+// (v = [.., a_i at j = i, doubled limbs above]); the rest of the row is the usual Montgomery step.
+template <class F, int I>
+PSD_DEV void sqr_row(uint32_t* x, uint32_t* y, const uint32_t* v, uint32_t ai) {
+    // odd-index entries ride the sliding (hi-aligned) chain, even-index entries the lo-aligned one
+    mad4_slide_from<I / 2>(x, y[0], v[1], v[3], v[5], v[7], ai);
+    mad4_from<(I + 1) / 2>(y, v[0], v[2], v[4], v[6], ai, x[7]);
+    const uint32_t m = y[0] * np0<F>();
+    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
+}
+
+// r = a^2 * 2^-256 mod p with 36 wide multiplies for the product instead of 64: each off-diagonal
+// product a_i*a_j (i<j) is taken once against the doubled operand d = 2a (limb j of d carries the top
+// bit of a_{j-1}; for row i that bit is masked off limb i+1, so the row adds
+// a_i * (a_i*2^(32i) + 2*(a >> 32(i+1)) << 32(i+1))).  Needs 3p < 2^256 for the 9-limb window
+// (row multiplicand < 2a < 2p, plus m*p), i.e. BN254 Fr; F::kSqrNineLimb says so.
+template <class F>
+PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
+    uint32_t d[8];
+#if !defined(PSD_HOST_EMU)
+#pragma unroll
+    for (int k = 1; k < 8; k++) d[k] = __funnelshift_l(a[k - 1], a[k], 1);
+#else
+    for (int k = 1; k < 8; k++) d[k] = (a[k] << 1) | (a[k - 1] >> 31);
+#endif
+    d[0] = 0;
+    uint32_t e[8], o[8];
+    {   // row 0: all eight products
+        const uint32_t d1 = d[1] & 0xfffffffeu;
+        mul4(e, a[0], d[2], d[4], d[6], a[0]);
+        mul4(o, d1, d[3], d[5], d[7], a[0]);
+        const uint32_t m = e[0] * np0<F>();
+        mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+        mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
+    }
+    uint32_t v[8];
+#define PSD_SQR_ROW(I, X, Y)                                        \
+    {                                                               \
+        _Pragma("unroll") for (int k = 0; k < 8; k++) v[k] = d[k];  \
+        v[I] = a[I];                                                \
+        if (I < 7) v[I + 1] = d[I + 1] & 0xfffffffeu;               \
+        sqr_row<F, I>(X, Y, v, a[I]);                               \
+    }
+    PSD_SQR_ROW(1, e, o)
+    PSD_SQR_ROW(2, o, e)
+    PSD_SQR_ROW(3, e, o)
+    PSD_SQR_ROW(4, o, e)
+    PSD_SQR_ROW(5, e, o)
+    PSD_SQR_ROW(6, o, e)
+    PSD_SQR_ROW(7, e, o)
+#undef PSD_SQR_ROW
+    uint32_t s[8];
+    merge8(s, e, o);
+    cond_sub_p<F>(r, s);
+}
+
+// Squaring entry point used by the S-box: dedicated squaring where its bound holds.
+template <class F>
+PSD_DEV void fp_sqr(uint32_t* r, const uint32_t* a) {
+    if (F::kBits == 254) mont_sqr<F>(r, a);
+    else mont_mul<F>(r, a, a);
+}
+
 // x^alpha for the S-box (apply_s_box, poseidon/mod.rs:63-74).  ark-ff's `pow` is an MSB-first
 // square-and-multiply; exponentiation is exponentiation, so any chain gives the same residue.
 template <class F>
 PSD_DEV void fp_pow5(uint32_t* r, const uint32_t* x) {
     uint32_t x2[8], x4[8];
-    mont_mul<F>(x2, x, x);
-    mont_mul<F>(x4, x2, x2);
+    fp_sqr<F>(x2, x);
+    fp_sqr<F>(x4, x2);
     mont_mul<F>(r, x4, x);
 }
 
@@ -364,7 +571,7 @@ PSD_DEV void fp_pow_u64(uint32_t* r, const uint32_t* x, uint64_t alpha, const ui
     bool started = false;
 #pragma unroll 1
     for (int bit = 63; bit >= 0; bit--) {
-        if (started) mont_mul<F>(acc, acc, acc);
+        if (started) fp_sqr<F>(acc, acc);
         if ((alpha >> bit) & 1) {
             if (started) {
                 mont_mul<F>(acc, acc, x);

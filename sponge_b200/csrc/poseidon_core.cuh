@@ -46,10 +46,10 @@ PSD_DEV void sbox(uint32_t* x, const PermDesc& d) {
         fp_pow5<F>(x, x);
     } else if (ALPHA == 17) {
         uint32_t y[8];
-        mont_mul<F>(y, x, x);
-        mont_mul<F>(y, y, y);
-        mont_mul<F>(y, y, y);
-        mont_mul<F>(y, y, y);
+        fp_sqr<F>(y, x);
+        fp_sqr<F>(y, y);
+        fp_sqr<F>(y, y);
+        fp_sqr<F>(y, y);
         mont_mul<F>(x, y, x);
     } else {
         const uint64_t alpha = ((uint64_t)d.alpha_hi << 32) | d.alpha_lo;

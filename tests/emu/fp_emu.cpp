@@ -111,3 +111,10 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     if (rc) return rc;
     return (variant == 1 && !d.opt_ok) ? 1 : 0;
 }
+
+extern "C" void emu_mont_sqr(int field, uint32_t* r, const uint32_t* a, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        if (field == 0) mont_sqr<Bn254Fr>(r + 8 * i, a + 8 * i);
+        else fp_sqr<Bls12381Fr>(r + 8 * i, a + 8 * i);
+    }
+}
