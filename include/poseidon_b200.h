@@ -235,8 +235,8 @@ psd_status psd_synth_fill(psd_ctx* ctx, uint64_t* dev_elems, size_t n, uint64_t 
 /* Number of kernels this library has launched in the calling process (monotonic). */
 uint64_t psd_kernel_launch_count(void);
 /* K0: sustained integer-multiply throughput of the device the context lives on.  Runs a
- * dependent-free IMAD.WIDE.U32 (kind 0), IMAD lo (kind 1) or the library's own mont_mul (kind 2)
- * loop on every SM and returns multiply (or modmul) results per second. */
+ * IMAD.WIDE.U32 (kind 0), IMAD lo (kind 1), the library's own Montgomery product (kind 2) or
+ * squaring (kind 3) loop on every SM and returns results per second. */
 psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* elapsed_ms);
 /* Select the permutation kernel variant for subsequent calls on this context:
  * 0 = dense (ark -> S-box -> dense MDS every round, the reference's operation order),

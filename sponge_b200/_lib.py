@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libposeidon_b200.so")
+# POSEIDON_B200_LIB overrides the library path (tuning builds); the default is the in-tree build.
+LIB_PATH = os.environ.get("POSEIDON_B200_LIB") or os.path.join(_HERE, "lib", "libposeidon_b200.so")
 
 PSD_OK, PSD_ERR_ARG, PSD_ERR_SHAPE, PSD_ERR_NONCANONICAL, PSD_ERR_CUDA, PSD_ERR_UNSUPPORTED, PSD_ERR_NOMEM = range(7)
 FIELD_BN254_FR, FIELD_BLS12_381_FR = 0, 1

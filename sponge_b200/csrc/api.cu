@@ -719,7 +719,7 @@ psd_status psd_synth_fill(psd_ctx* ctx, uint64_t* dev_elems, size_t n, uint64_t 
 
 psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* elapsed_ms) {
     if (!ctx || !per_second) return fail(PSD_ERR_ARG, "null argument");
-    if (kind < 0 || kind > 2) return fail(PSD_ERR_ARG, "kind must be 0, 1 or 2");
+    if (kind < 0 || kind > 3) return fail(PSD_ERR_ARG, "kind must be 0..3");
     DeviceGuard guard(ctx->device);
     uint32_t* scratch = nullptr;
     PSD_CUDA(cudaMalloc(&scratch, 1024 * 4));
@@ -729,9 +729,9 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
     psd_status result = PSD_OK;
     float ms = 0;
     LaunchCfg cfg;
-    cfg.block = kind == 2 ? 128 : 256;
-    cfg.grid = ctx->sm_count * (kind == 2 ? 8 : 8);
-    const uint32_t iters = kind == 2 ? 4096 : 16384;
+    cfg.block = kind >= 2 ? 128 : 256;
+    cfg.grid = ctx->sm_count * 8;
+    const uint32_t iters = kind >= 2 ? 4096 : 16384;
     do {
 #define K0_CUDA(call)                                                                           \
     if ((cudaError_t)(call) != cudaSuccess) {                                                   \
@@ -751,7 +751,7 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
         K0_CUDA(cudaEventElapsedTime(&ms, e0, e1));
         g_launches += 7;
         const double threads = (double)cfg.grid * cfg.block;
-        const double per_thread = kind == 2 ? 2.0 * iters : 64.0 * iters;
+        const double per_thread = kind >= 2 ? 2.0 * iters : 64.0 * iters;
         *per_second = threads * per_thread * reps / (ms * 1e-3);
         if (elapsed_ms) *elapsed_ms = ms / reps;
 #undef K0_CUDA

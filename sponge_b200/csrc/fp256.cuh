@@ -485,7 +485,8 @@ PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8
 // Largest N for which mont_dot's no-overflow condition (N+1)*p < 2^256 holds.
 template <class F>
 struct DotLimit {
-    static constexpr int kMax = (F::kBits == 254) ? 4 : 1;
+    static constexpr int kMax = 4;                      // terms per lazily reduced group
+    static constexpr bool kWide = (F::kBits != 254);    // needs the 10-limb window (mont_dot_w)
 };
 
 // One CIOS row of the squaring: only the products a_i * v_j with j >= i are added
@@ -545,11 +546,185 @@ PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
     cond_sub_p<F>(r, s);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Wide-window variants.  For BLS12-381 Fr (p ~ 0.45 * 2^256) the running window of a lazily reduced
+// dot product or of the squaring can exceed 9 limbs, so a tenth limb `top` (column 9) collects the
+// carries out of column 8 and re-enters at the top pair when the window slides.  The result can be
+// up to 3p (a 257-bit value); reduce_3p brings it back to [0,p).
+// ------------------------------------------------------------------------------------------------
+// x7 += c; top += carry
+PSD_DEV void add_carry2(uint32_t& x7, uint32_t& top, uint32_t c) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %0, %2;\n\taddc.u32 %1, %1, 0;" : "+r"(x7), "+r"(top) : "r"(c));
+#else
+    uint64_t s = (uint64_t)x7 + c;
+    x7 = (uint32_t)s;
+    top += (uint32_t)(s >> 32);
+#endif
+}
+// lo-aligned chain (columns 0..7): carry -> column 8 (x7) -> column 9 (top)
+template <int S>
+PSD_DEV void mad4w_lo(uint32_t* y, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b, uint32_t& x7,
+                      uint32_t& top) {
+    if (S >= 4) return;
+    uint32_t c = 0;
+    mad4_from<S>(y, a0, a1, a2, a3, b, c);
+    add_carry2(x7, top, c);
+}
+// window slide: as mad4_slide_from, then the old column 9 re-enters at column 8 and the new
+// column 9 is the carry out of it
+template <int S>
+PSD_DEV void mad4w_slide(uint32_t* x, uint32_t& y0, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b,
+                         uint32_t& top) {
+    mad4_slide_from<S>(x, y0, a0, a1, a2, a3, b);
+    const uint32_t old = top;
+    top = 0;
+    add_carry2(x[7], top, old);
+}
+// Montgomery step on a wide window
+template <class F>
+PSD_DEV void redc_step_w(uint32_t* x, uint32_t* y, uint32_t& top) {
+    const uint32_t m = y[0] * np0<F>();
+    mad4(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m, top);
+    mad4w_lo<0>(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7], top);
+}
+// r = (w + (z >> 32) + top * 2^256) mod p for a value below 3p
+template <class F>
+PSD_DEV void reduce_3p(uint32_t* r, const uint32_t* w, const uint32_t* z, uint32_t top) {
+    uint32_t s[8], c8;
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %9, %17;\n\t"
+        "addc.cc.u32 %1, %10, %18;\n\t"
+        "addc.cc.u32 %2, %11, %19;\n\t"
+        "addc.cc.u32 %3, %12, %20;\n\t"
+        "addc.cc.u32 %4, %13, %21;\n\t"
+        "addc.cc.u32 %5, %14, %22;\n\t"
+        "addc.cc.u32 %6, %15, %23;\n\t"
+        "addc.cc.u32 %7, %16, 0;\n\t"
+        "addc.u32 %8, %24, 0;"
+        : "=r"(s[0]), "=r"(s[1]), "=r"(s[2]), "=r"(s[3]), "=r"(s[4]), "=r"(s[5]), "=r"(s[6]), "=r"(s[7]), "=r"(c8)
+        : "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]),
+          "r"(z[1]), "r"(z[2]), "r"(z[3]), "r"(z[4]), "r"(z[5]), "r"(z[6]), "r"(z[7]), "r"(top));
+#else
+    uint64_t c = 0;
+    for (int k = 0; k < 8; k++) {
+        uint64_t t = (uint64_t)w[k] + (k < 7 ? z[k + 1] : 0) + c;
+        s[k] = (uint32_t)t;
+        c = t >> 32;
+    }
+    c8 = top + (uint32_t)c;
+#endif
+    // step 1: v = c8*2^256 + s < 3p.  d = s - p mod 2^256; take d if c8 is set (then v - p < 2^256) or s >= p
+    uint32_t d[8], borrow;
+#if !defined(PSD_HOST_EMU)
+    asm("sub.cc.u32 %0, %9, %17;\n\t"
+        "subc.cc.u32 %1, %10, %18;\n\t"
+        "subc.cc.u32 %2, %11, %19;\n\t"
+        "subc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\t"
+        "subc.cc.u32 %5, %14, %22;\n\t"
+        "subc.cc.u32 %6, %15, %23;\n\t"
+        "subc.cc.u32 %7, %16, %24;\n\t"
+        "subc.u32 %8, 0, 0;"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(borrow)
+        : "r"(s[0]), "r"(s[1]), "r"(s[2]), "r"(s[3]), "r"(s[4]), "r"(s[5]), "r"(s[6]), "r"(s[7]),
+          "r"(plimb<F, 0>()), "r"(plimb<F, 1>()), "r"(plimb<F, 2>()), "r"(plimb<F, 3>()), "r"(plimb<F, 4>()),
+          "r"(plimb<F, 5>()), "r"(plimb<F, 6>()), "r"(plimb<F, 7>()));
+#else
+    const uint32_t p[8] = {F::P0, F::P1, F::P2, F::P3, F::P4, F::P5, F::P6, F::P7};
+    int64_t bc = 0;
+    for (int k = 0; k < 8; k++) {
+        int64_t t = (int64_t)s[k] - p[k] + bc;
+        d[k] = (uint32_t)t;
+        bc = t >> 32;
+    }
+    borrow = (uint32_t)bc;
+#endif
+    const bool take = (c8 != 0) || (borrow == 0);
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = take ? d[k] : s[k];
+    // step 2: v < 2p
+    cond_sub_p<F>(r, v);
+}
+
+// Lazily reduced dot product with the wide window: any field here, N <= 4 (result < 3p).
+template <class F, int N>
+PSD_DEV void mont_dot_w(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8]) {
+    uint32_t e[8], o[8], top = 0;
+    mul4(e, a[0][0], a[0][2], a[0][4], a[0][6], b[0][0]);
+    mul4(o, a[0][1], a[0][3], a[0][5], a[0][7], b[0][0]);
+#pragma unroll
+    for (int j = 1; j < N; j++) {
+        mad4(o, a[j][1], a[j][3], a[j][5], a[j][7], b[j][0], top);
+        mad4w_lo<0>(e, a[j][0], a[j][2], a[j][4], a[j][6], b[j][0], o[7], top);
+    }
+    redc_step_w<F>(o, e, top);
+#pragma unroll
+    for (int i = 1; i < 8; i++) {
+        uint32_t* x = (i & 1) ? e : o;
+        uint32_t* y = (i & 1) ? o : e;
+        mad4w_slide<0>(x, y[0], a[0][1], a[0][3], a[0][5], a[0][7], b[0][i], top);
+        mad4w_lo<0>(y, a[0][0], a[0][2], a[0][4], a[0][6], b[0][i], x[7], top);
+#pragma unroll
+        for (int j = 1; j < N; j++) {
+            mad4(x, a[j][1], a[j][3], a[j][5], a[j][7], b[j][i], top);
+            mad4w_lo<0>(y, a[j][0], a[j][2], a[j][4], a[j][6], b[j][i], x[7], top);
+        }
+        redc_step_w<F>(x, y, top);
+    }
+    reduce_3p<F>(r, e, o, top);
+}
+
+template <class F, int I>
+PSD_DEV void sqr_row_w(uint32_t* x, uint32_t* y, const uint32_t* v, uint32_t ai, uint32_t& top) {
+    mad4w_slide<I / 2>(x, y[0], v[1], v[3], v[5], v[7], ai, top);
+    mad4w_lo<(I + 1) / 2>(y, v[0], v[2], v[4], v[6], ai, x[7], top);
+    redc_step_w<F>(x, y, top);
+}
+
+// mont_sqr with the wide window (same product schedule): any field with p < 2^255.
+template <class F>
+PSD_DEV void mont_sqr_w(uint32_t* r, const uint32_t* a) {
+    uint32_t d[8];
+#if !defined(PSD_HOST_EMU)
+#pragma unroll
+    for (int k = 1; k < 8; k++) d[k] = __funnelshift_l(a[k - 1], a[k], 1);
+#else
+    for (int k = 1; k < 8; k++) d[k] = (a[k] << 1) | (a[k - 1] >> 31);
+#endif
+    d[0] = 0;
+    uint32_t e[8], o[8], top = 0;
+    {
+        const uint32_t d1 = d[1] & 0xfffffffeu;
+        mul4(e, a[0], d[2], d[4], d[6], a[0]);
+        mul4(o, d1, d[3], d[5], d[7], a[0]);
+        redc_step_w<F>(o, e, top);
+    }
+    uint32_t v[8];
+#define PSD_SQR_ROW_W(I, X, Y)                                      \
+    {                                                               \
+        _Pragma("unroll") for (int k = 0; k < 8; k++) v[k] = d[k];  \
+        v[I] = a[I];                                                \
+        if (I < 7) v[I + 1] = d[I + 1] & 0xfffffffeu;               \
+        sqr_row_w<F, I>(X, Y, v, a[I], top);                        \
+    }
+    PSD_SQR_ROW_W(1, e, o)
+    PSD_SQR_ROW_W(2, o, e)
+    PSD_SQR_ROW_W(3, e, o)
+    PSD_SQR_ROW_W(4, o, e)
+    PSD_SQR_ROW_W(5, e, o)
+    PSD_SQR_ROW_W(6, o, e)
+    PSD_SQR_ROW_W(7, e, o)
+#undef PSD_SQR_ROW_W
+    reduce_3p<F>(r, e, o, top);
+}
+
 // Squaring entry point used by the S-box: dedicated squaring where its bound holds.
 template <class F>
 PSD_DEV void fp_sqr(uint32_t* r, const uint32_t* a) {
     if (F::kBits == 254) mont_sqr<F>(r, a);
-    else mont_mul<F>(r, a, a);
+    else mont_sqr_w<F>(r, a);
 }
 
 // x^alpha for the S-box (apply_s_box, poseidon/mod.rs:63-74).  ark-ff's `pow` is an MSB-first

@@ -112,8 +112,9 @@ __global__ void __launch_bounds__(256) imad_lo_kernel(uint32_t* scratch, uint32_
     if (s == 0x12345678u) scratch[tid & 1023] = s;
 }
 
-// Two independent chains of the library's own Montgomery product per thread.
-template <class F>
+// Two independent chains of the library's own Montgomery product (SQR = false) or squaring (true)
+// per thread.
+template <class F, bool SQR>
 __global__ void __launch_bounds__(128) modmul_kernel(uint32_t* scratch, uint32_t iters) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t x[8], y[8], c[8];
@@ -128,8 +129,13 @@ __global__ void __launch_bounds__(128) modmul_kernel(uint32_t* scratch, uint32_t
     c[7] &= 0x0fffffffu;
 #pragma unroll 1
     for (uint32_t it = 0; it < iters; it++) {
-        mont_mul<F>(x, x, c);
-        mont_mul<F>(y, y, c);
+        if (SQR) {
+            fp_sqr<F>(x, x);
+            fp_sqr<F>(y, y);
+        } else {
+            mont_mul<F>(x, x, c);
+            mont_mul<F>(y, y, c);
+        }
     }
     uint32_t s = 0;
 #pragma unroll
@@ -163,8 +169,10 @@ int launch_imad_peak(int field, int kind, uint32_t* scratch, uint32_t iters, Lau
     cudaStream_t s = (cudaStream_t)stream;
     if (kind == 0) imad_wide_kernel<<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
     else if (kind == 1) imad_lo_kernel<<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
-    else if (field == 0) modmul_kernel<Bn254Fr><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
-    else modmul_kernel<Bls12381Fr><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
+    else if (kind == 2 && field == 0) modmul_kernel<Bn254Fr, false><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
+    else if (kind == 2) modmul_kernel<Bls12381Fr, false><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
+    else if (field == 0) modmul_kernel<Bn254Fr, true><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
+    else modmul_kernel<Bls12381Fr, true><<<cfg.grid, cfg.block, 0, s>>>(scratch, iters);
     return (int)cudaGetLastError();
 }
 

@@ -122,6 +122,22 @@ PSD_DEV void permute_dense(uint32_t (&st)[T][8], const PermDesc& d) {
 //  * every matrix row is a lazily reduced dot product (mont_dot) where the field allows it.
 // Results are identical to permute_dense: the values are the same field elements, fully reduced.
 // ------------------------------------------------------------------------------------------------
+// part = sum_{j<n} a[j]*cf[j] (n <= G <= 4 known at compile time after unrolling)
+template <class F, int G>
+PSD_DEV void dot_group(uint32_t* part, const uint32_t (*a)[8], const uint32_t (*cf)[8], int n) {
+    if (n == 1) {
+        mont_mul<F>(part, a[0], cf[0]);
+    } else if (DotLimit<F>::kWide) {
+        if (n == 2) mont_dot_w<F, 2>(part, a, cf);
+        else if (n == 3) mont_dot_w<F, (G >= 3 ? 3 : 1)>(part, a, cf);
+        else mont_dot_w<F, (G >= 4 ? 4 : 1)>(part, a, cf);
+    } else {
+        if (n == 2) mont_dot<F, 2>(part, a, cf);
+        else if (n == 3) mont_dot<F, (G >= 3 ? 3 : 1)>(part, a, cf);
+        else mont_dot<F, (G >= 4 ? 4 : 1)>(part, a, cf);
+    }
+}
+
 template <class F, int T>
 PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
     // r = sum_{j<T} st[j] * c_pool[coeff_off + 8j ...], in groups of at most DotLimit<F>::kMax terms
@@ -136,10 +152,7 @@ PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
 #pragma unroll
             for (int k = 0; k < 8; k++) cf[j][k] = (j0 + j < T) ? c_pool[coeff_off + (j0 + j) * 8 + k] : 0u;
         const int n = (T - j0 < G) ? (T - j0) : G;
-        if (n == 1) mont_mul<F>(part, st[j0], cf[0]);
-        else if (n == 2) mont_dot<F, 2>(part, st + j0, cf);
-        else if (n == 3) mont_dot<F, 3>(part, st + j0, cf);
-        else mont_dot<F, (G >= 4 ? 4 : 1)>(part, st + j0, cf);
+        dot_group<F, G>(part, st + j0, cf, n);
         if (first) {
 #pragma unroll
             for (int k = 0; k < 8; k++) r[k] = part[k];
@@ -196,10 +209,7 @@ PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t
                     cf[j][k] = (jj >= T) ? 0u : (jj == 0 ? c_pool[d.mds_off + k] : c_pool[off + jj * 8 + k]);
                 }
             const int n = (T - j0 < G) ? (T - j0) : G;
-            if (n == 1) mont_mul<F>(part, st[j0], cf[0]);
-            else if (n == 2) mont_dot<F, 2>(part, st + j0, cf);
-            else if (n == 3) mont_dot<F, 3>(part, st + j0, cf);
-            else mont_dot<F, (G >= 4 ? 4 : 1)>(part, st + j0, cf);
+            dot_group<F, G>(part, st + j0, cf, n);
             if (first) {
 #pragma unroll
                 for (int k = 0; k < 8; k++) n0[k] = part[k];

@@ -57,8 +57,16 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
     }
 }
 
+// Resident 128-thread blocks per SM the register allocation is steered towards (the multiplier pipe
+// needs >= 4 warps per scheduler to stay busy; see profiles/).  Overridable for tuning runs.
+// Measured on B200 (bench c2/c3, min blocks 3..7): t=3 is flat within 2 % (125-128 M perm/s), t=5 is
+// best when ptxas is left alone (138 registers, no spills), so only t<=3 gets a hint.
+#ifndef PSD_MIN_BLOCKS
+#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 5 : 1)
+#endif
+
 template <class F, int T, int ALPHA, int VARIANT>
-__global__ void __launch_bounds__(128) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+__global__ void __launch_bounds__(128, PSD_MIN_BLOCKS(T)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
     const PermDesc& d = a.d;
     const uint32_t rate = d.rate, cap = d.capacity;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;

@@ -118,3 +118,23 @@ extern "C" void emu_mont_sqr(int field, uint32_t* r, const uint32_t* a, size_t n
         else fp_sqr<Bls12381Fr>(r + 8 * i, a + 8 * i);
     }
 }
+
+extern "C" void emu_mont_dot_w(int field, int n_terms, uint32_t* r, const uint32_t* a, const uint32_t* b, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        const uint32_t(*ap)[8] = reinterpret_cast<const uint32_t(*)[8]>(a + i * n_terms * 8);
+        const uint32_t(*bp)[8] = reinterpret_cast<const uint32_t(*)[8]>(b + i * n_terms * 8);
+#define PSD_CASE(N)                                                             \
+    case N:                                                                     \
+        if (field == 0) mont_dot_w<Bn254Fr, N>(r + 8 * i, ap, bp);              \
+        else mont_dot_w<Bls12381Fr, N>(r + 8 * i, ap, bp);                      \
+        break;
+        switch (n_terms) { PSD_CASE(1) PSD_CASE(2) PSD_CASE(3) PSD_CASE(4) }
+#undef PSD_CASE
+    }
+}
+extern "C" void emu_mont_sqr_w(int field, uint32_t* r, const uint32_t* a, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        if (field == 0) mont_sqr_w<Bn254Fr>(r + 8 * i, a + 8 * i);
+        else mont_sqr_w<Bls12381Fr>(r + 8 * i, a + 8 * i);
+    }
+}

@@ -231,3 +231,34 @@ def test_cpp_wrapper_compiles_and_refuses_without_gpu(S):
         assert r.returncode == 0, r.stdout
     else:
         assert r.returncode == 3 and "no CPU path" in r.stdout
+
+
+@pytest.mark.parametrize("field", [0, 1])
+def test_squaring_and_wide_window_host_model(emu, ref, field):
+    """Dedicated squaring (36 wide multiplies) and the 10-limb-window variants used for BLS12-381
+    (lazy dot products whose running sum exceeds 9 limbs, results up to 3p), worst-case operands."""
+    p = ref.BN254_FR if field == 0 else ref.BLS12_381_FR
+    rng = random.Random(100 + field)
+    rinv = pow(1 << 256, -1, p)
+    n = 4000
+    A = [rng.randrange(p) for _ in range(n)]
+    A[:8] = [0, 1, p - 1, p - 2, (1 << 253) - 1, 1 << 253, 0xffffffff, 1 << 32]
+    a = to_limbs(A).view(np.uint32)
+    exp = [x * x * rinv % p for x in A]
+    for fn in (emu.emu_mont_sqr, emu.emu_mont_sqr_w):
+        r = np.zeros_like(a)
+        fn(field, C.c_void_p(r.ctypes.data), C.c_void_p(a.ctypes.data), C.c_size_t(n))
+        assert to_ints(r.view(np.uint64)) == exp
+    for n_terms in (1, 2, 3, 4):
+        m = 1500
+        AA = [[rng.randrange(p) for _ in range(n_terms)] for _ in range(m)]
+        BB = [[rng.randrange(p) for _ in range(n_terms)] for _ in range(m)]
+        AA[0] = [p - 1] * n_terms
+        BB[0] = [p - 1] * n_terms
+        AA[1] = [0] * n_terms
+        av = to_limbs(v for r_ in AA for v in r_).view(np.uint32)
+        bv = to_limbs(v for r_ in BB for v in r_).view(np.uint32)
+        r = np.zeros(m * 8, dtype=np.uint32)
+        emu.emu_mont_dot_w(field, n_terms, C.c_void_p(r.ctypes.data), C.c_void_p(av.ctypes.data),
+                           C.c_void_p(bv.ctypes.data), C.c_size_t(m))
+        assert to_ints(r.view(np.uint64)) == [sum(x * y for x, y in zip(ra, rb)) * rinv % p for ra, rb in zip(AA, BB)]
