@@ -62,7 +62,7 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // Measured on B200 (bench c2/c3, min blocks 3..7): t=3 is flat within 2 % (125-128 M perm/s), t=5 is
 // best when ptxas is left alone (138 registers, no spills), so only t<=3 gets a hint.
 #ifndef PSD_MIN_BLOCKS
-#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 5 : 1)
+#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 5 : 0)   /* 0 = no hint */
 #endif
 
 template <class F, int T, int ALPHA, int VARIANT>
