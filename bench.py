@@ -412,8 +412,11 @@ def main():
     # this run.  IMAD.WIDE.U32 (the 32x32->64 form a multi-limb product needs) issues at less than half
     # of that on B200 (k0.imad_wide_per_s), so a kernel that executes all W_alg multiplies as IMAD.WIDE
     # tops out near 0.45; the optimised kernel gets above that by executing fewer multiplies than W_alg.
+    # DRAM bytes per launch from the committed ncu --set full capture of this exact workload
+    # (profiles/r1_c2_opt_v2_sqr_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
+    traffic = 3.199e9 if (name == "c2" and log_n == 24) else None
     roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_lo / 1e9, unit="Gimul/s",
-                    frac=achieved_imul / imad_lo, traffic=None,
+                    frac=achieved_imul / imad_lo, traffic=traffic,
                     w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
                     peak_source="K0 probe in this run: sustained 32-bit IMAD results/s on all SMs "
                                 "(integer-multiply pipe issue rate)",
