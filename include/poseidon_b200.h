@@ -238,9 +238,10 @@ uint64_t psd_kernel_launch_count(void);
  * IMAD.WIDE.U32 (kind 0), IMAD lo (kind 1), the library's own Montgomery product (kind 2) or
  * squaring (kind 3) loop on every SM and returns results per second. */
 psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* elapsed_ms);
-/* Select the permutation kernel variant for subsequent calls on this context:
+/* Select the permutation kernel variant for subsequent calls on this context (same results):
  * 0 = dense (ark -> S-box -> dense MDS every round, the reference's operation order),
- * 1 = optimised (default; same results). */
+ * 1 = optimised, fully unrolled rounds,
+ * 2 = optimised, compact rolled phases (default: smallest hot loop, fastest on B200). */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
 
 #ifdef __cplusplus

@@ -135,7 +135,7 @@ struct psd_ctx {
     PermDesc desc{};
     uint32_t pool_off = 0, pool_len = 0;
     bool pool_held = false;
-    int variant = 1;
+    int variant = 2;
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;
@@ -241,7 +241,7 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
 }
 
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
-    const int variant = (ctx->variant == 1 && ctx->desc.opt_ok) ? 1 : 0;
+    const int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
     const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
@@ -611,7 +611,7 @@ psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
 
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
     if (!ctx) return fail(PSD_ERR_ARG, "null context");
-    if (variant < 0 || variant > 1) return fail(PSD_ERR_ARG, "variant must be 0 or 1");
+    if (variant < 0 || variant > 2) return fail(PSD_ERR_ARG, "variant must be 0, 1 or 2");
     ctx->variant = variant;
     return PSD_OK;
 }

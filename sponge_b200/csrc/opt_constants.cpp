@@ -141,6 +141,7 @@ void append_optimised_constants(const HostField& f, uint32_t t, uint32_t full_ro
     d.sparse_off = (uint32_t)img.size();
     for (uint32_t i = 0; i < rp; i++) {
         push_fe(img, k_lane0[i]);
+        push_fe(img, mds[0]);   // M00, so that the row-0 coefficients (M00, w_1, ..) are contiguous
         for (uint32_t j = 0; j < n; j++) push_fe(img, w[i][j]);
         for (uint32_t j = 0; j < n; j++) push_fe(img, v[i][j]);
     }

@@ -36,7 +36,7 @@ struct PermDesc {
     // optimised form (see opt_constants.cpp); valid when opt_ok != 0
     uint32_t opt_ok;
     uint32_t pre_mds_off;   // [T][T][8]  matrix of the last full round before the partial rounds
-    uint32_t sparse_off;    // [partial][2T-1][8]: k, w_1..w_{T-1}, v_1..v_{T-1} per partial round
+    uint32_t sparse_off;    // [partial][2T][8]: k, M00, w_1..w_{T-1}, v_1..v_{T-1} per partial round
     uint32_t post_ark_off;  // [T][8]     round constants of the first full round after the partial rounds
 };
 
@@ -184,7 +184,7 @@ PSD_DEV void full_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t ar
 
 template <class F, int T, int ALPHA>
 PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t off) {
-    // off -> [k][w_1..w_{T-1}][v_1..v_{T-1}]
+    // off -> [k][M00][w_1..w_{T-1}][v_1..v_{T-1}]
     {
         uint32_t c[8];
 #pragma unroll
@@ -192,39 +192,15 @@ PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t
         fp_add<F>(st[0], st[0], c);
         sbox<F, ALPHA>(st[0], d);
     }
-    // s0' = M00*s0 + sum w_j s_j  : coefficients (M00, w_1, ...) -- M00 is mds[0][0]
+    // s0' = M00*s0 + sum w_j s_j  : coefficients (M00, w_1, ...) stored contiguously after k
     uint32_t n0[8];
-    {
-        constexpr int G = DotLimit<F>::kMax;
-        bool first = true;
-#pragma unroll
-        for (int j0 = 0; j0 < T; j0 += G) {
-            uint32_t part[8];
-            uint32_t cf[G][8];
-#pragma unroll
-            for (int j = 0; j < G; j++)
-#pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    const int jj = j0 + j;
-                    cf[j][k] = (jj >= T) ? 0u : (jj == 0 ? c_pool[d.mds_off + k] : c_pool[off + jj * 8 + k]);
-                }
-            const int n = (T - j0 < G) ? (T - j0) : G;
-            dot_group<F, G>(part, st + j0, cf, n);
-            if (first) {
-#pragma unroll
-                for (int k = 0; k < 8; k++) n0[k] = part[k];
-                first = false;
-            } else {
-                fp_add<F>(n0, n0, part);
-            }
-        }
-    }
+    row_dot<F, T>(n0, st, off + 8);
     // s_j' = s_j + v_j * s0
 #pragma unroll
     for (int j = 1; j < T; j++) {
         uint32_t v[8], prod[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = c_pool[off + (T - 1 + j) * 8 + k];
+        for (int k = 0; k < 8; k++) v[k] = c_pool[off + (T + j) * 8 + k];
         mont_mul<F>(prod, st[0], v);
         fp_add<F>(st[j], st[j], prod);
     }
@@ -244,7 +220,114 @@ PSD_DEV void permute_opt(uint32_t (&st)[T][8], const PermDesc& d) {
             const uint32_t mds = (r + 1 == first_partial && d.partial) ? d.pre_mds_off : d.mds_off;
             full_round_opt<F, T, ALPHA>(st, d, ark, mds);
         } else {
-            partial_round_opt<F, T, ALPHA>(st, d, d.sparse_off + (r - first_partial) * (2 * T - 1) * 8);
+            partial_round_opt<F, T, ALPHA>(st, d, d.sparse_off + (r - first_partial) * (2 * T) * 8);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Compact optimised permutation (VARIANT 2): the same arithmetic as permute_opt, but every round is
+// run as three short rolled phases so that only ONE copy each of the S-box, the row dot product and
+// the lane multiply-add exists in the hot loop (about a third of the code of permute_opt; ncu showed
+// 21 % of warp stalls of permute_opt as no_instruction, i.e. instruction fetch).  Lanes are rotated
+// through fixed register names with moves instead of being indexed.
+//   phase A: nA x { s0 += c_i; s0 <- s0^alpha; [rotate lanes] }        nA = T (full) | 1 (partial)
+//   phase B: nB x { t = <coeff row i, s>; shift t into n }             nB = T (full) | 1 (partial)
+//   phase C: partial only, (T-1) x { s1 += v_j * s0; rotate lanes 1..T-1 }
+// ------------------------------------------------------------------------------------------------
+template <class F, int ALPHA>
+PSD_DEV void sbox_compact(uint32_t* x, const PermDesc& d) {
+    if (ALPHA == 5 || ALPHA == 17) {
+        uint32_t y[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) y[k] = x[k];
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F>(y, y);
+        mont_mul<F>(x, y, x);
+    } else {
+        sbox<F, ALPHA>(x, d);
+    }
+}
+
+template <class F, int T, int ALPHA>
+PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
+    const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (uint32_t r = 0; r < d.total; r++) {
+        const bool full = (r < first_partial || r >= first_post);
+        const uint32_t sp = d.sparse_off + (r - first_partial) * (2 * T) * 8;   // only meaningful when !full
+        const uint32_t ark = full ? ((r == first_post && d.partial) ? d.post_ark_off : d.ark_off + r * T * 8) : sp;
+        const uint32_t coeff = full ? ((r + 1 == first_partial && d.partial) ? d.pre_mds_off : d.mds_off) : sp + 8;
+        const uint32_t n_iter = full ? T : 1;
+        // phase A
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (uint32_t i = 0; i < n_iter; i++) {
+            uint32_t c[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) c[k] = c_pool[ark + i * 8 + k];
+            fp_add<F>(st[0], st[0], c);
+            sbox_compact<F, ALPHA>(st[0], d);
+            if (full) {   // rotate left: the next lane moves into position 0
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t t0 = st[0][k];
+#pragma unroll
+                    for (int l = 0; l + 1 < T; l++) st[l][k] = st[l + 1][k];
+                    st[T - 1][k] = t0;
+                }
+            }
+        }
+        // phase B
+        uint32_t nw[T][8];
+#pragma unroll
+        for (int l = 0; l < T; l++)
+#pragma unroll
+            for (int k = 0; k < 8; k++) nw[l][k] = 0;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (uint32_t i = 0; i < n_iter; i++) {
+            uint32_t t[8];
+            row_dot<F, T>(t, st, coeff + i * T * 8);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+#pragma unroll
+                for (int l = 0; l + 1 < T; l++) nw[l][k] = nw[l + 1][k];
+                nw[T - 1][k] = t[k];
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int l = 0; l < T; l++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) st[l][k] = nw[l][k];
+        } else {
+            // phase C: s_j += v_j * s0 for j = 1..T-1, lanes 1..T-1 rotated through position 1
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+            for (uint32_t j = 0; j + 1 < T; j++) {
+                uint32_t v[8], prod[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) v[k] = c_pool[sp + (T + 1 + j) * 8 + k];
+                mont_mul<F>(prod, st[0], v);
+                fp_add<F>(st[1], st[1], prod);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t t1 = st[1][k];
+#pragma unroll
+                    for (int l = 1; l + 1 < T; l++) st[l][k] = st[l + 1][k];
+                    st[T - 1][k] = t1;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) st[0][k] = nw[T - 1][k];
         }
     }
 }

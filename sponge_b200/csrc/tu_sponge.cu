@@ -38,10 +38,12 @@ PSD_REG(0, 1)
 #if PSD_TU_T == 3 || PSD_TU_T == 5
 PSD_REG(5, 0)
 PSD_REG(5, 1)
+PSD_REG(5, 2)
 #endif
 #if PSD_TU_T == 3
 PSD_REG(17, 0)
 PSD_REG(17, 1)
+PSD_REG(17, 2)
 #endif
 
 }  // namespace psd

@@ -57,6 +57,7 @@ static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
         memcpy(s, st + i * T * 8, sizeof s);
         if (variant == 1 && d.opt_ok) permute_opt<F, T, ALPHA>(s, d);
         else if (variant == 2) permute_rolled<F, T, ALPHA>(s, d);
+        else if (variant == 3 && d.opt_ok) permute_opt_compact<F, T, ALPHA>(s, d);
         else permute_dense<F, T, ALPHA>(s, d);
         memcpy(st + i * T * 8, s, sizeof s);
     }
@@ -109,7 +110,7 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     int rc = field == 0 ? emu_perm_f<Bn254Fr>(d, t, alpha, variant, states, n)
                         : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
     if (rc) return rc;
-    return (variant == 1 && !d.opt_ok) ? 1 : 0;
+    return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }
 
 extern "C" void emu_mont_sqr(int field, uint32_t* r, const uint32_t* a, size_t n) {

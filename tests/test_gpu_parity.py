@@ -82,7 +82,7 @@ def test_permute_batch_matches_oracle(S, pairs, name):
     assert np.array_equal(unsoa(got_s, n, pr.t).reshape(-1, 4), exp)
 
 
-@pytest.mark.parametrize("name", ["bn254_t3", "bls_default_r2"])
+@pytest.mark.parametrize("name", ["bn254_t3", "bls_default_r2", "bn254_t5", "bls_fixture", "bn254_t4_cap2"])
 def test_permute_dense_variant_equals_optimised(S, pairs, name):
     pr = pairs(name)
     st = pr.orc.synth(2048 * pr.t, seed=0xA2)
@@ -90,7 +90,10 @@ def test_permute_dense_variant_equals_optimised(S, pairs, name):
     dense = pr.ctx.permute_batch(st.copy())
     pr.ctx.set_variant(1)
     opt = pr.ctx.permute_batch(st.copy())
+    pr.ctx.set_variant(2)
+    compact = pr.ctx.permute_batch(st.copy())
     assert np.array_equal(dense, opt)
+    assert np.array_equal(dense, compact)
     assert np.array_equal(dense, pr.orc.permute_batch(st.copy()))
 
 
