@@ -391,6 +391,71 @@ PSD_DEV void cond_sub_p(uint32_t* r, const uint32_t* a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// The Montgomery step  acc += m * p  split over the two accumulators:
+//   redc_hi: hi-aligned accumulator x (columns 1..8) += m * {p1,p3,p5,p7}, carry out added to *top
+//   redc_lo: lo-aligned accumulator y (columns 0..7) += m * {p0,p2,p4,p6}, carry out added to *c8
+// Generic fields use four wide multiplies each.  BLS12-381 Fr has p0 = 1 and p1 = 2^32 - 1, so
+// m*p0 = m and m*p1 = (m << 32) - m: those two products become two or three adds and the step
+// needs 6 wide multiplies instead of 8 (a quarter of the reduction's multiplier-pipe cycles).
+// ------------------------------------------------------------------------------------------------
+template <class F>
+PSD_DEV void redc_hi(uint32_t* x, uint32_t m, uint32_t& top) {
+#if !defined(PSD_HOST_EMU)
+    if (F::kBits == 255) {
+        asm("{\n\t"
+            ".reg .u32 t0, t1;\n\t"
+            "sub.cc.u32 t0, 0, %9;\n\t"
+            "subc.u32 t1, %9, 0;\n\t"
+            "add.cc.u32 %0, %0, t0;\n\t"
+            "addc.cc.u32 %1, %1, t1;\n\t"
+            "madc.lo.cc.u32 %2, %10, %9, %2;\n\t"
+            "madc.hi.cc.u32 %3, %10, %9, %3;\n\t"
+            "madc.lo.cc.u32 %4, %11, %9, %4;\n\t"
+            "madc.hi.cc.u32 %5, %11, %9, %5;\n\t"
+            "madc.lo.cc.u32 %6, %12, %9, %6;\n\t"
+            "madc.hi.cc.u32 %7, %12, %9, %7;\n\t"
+            "addc.u32 %8, %8, 0;\n\t"
+            "}"
+            : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]), "+r"(top)
+            : "r"(m), "r"(plimb<F, 3>()), "r"(plimb<F, 5>()), "r"(plimb<F, 7>()));
+        return;
+    }
+#endif
+    mad4(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m, top);
+}
+
+template <class F>
+PSD_DEV void redc_lo(uint32_t* y, uint32_t m, uint32_t& c8) {
+#if !defined(PSD_HOST_EMU)
+    if (F::kBits == 255) {
+        asm("add.cc.u32 %0, %0, %9;\n\t"
+            "addc.cc.u32 %1, %1, 0;\n\t"
+            "madc.lo.cc.u32 %2, %10, %9, %2;\n\t"
+            "madc.hi.cc.u32 %3, %10, %9, %3;\n\t"
+            "madc.lo.cc.u32 %4, %11, %9, %4;\n\t"
+            "madc.hi.cc.u32 %5, %11, %9, %5;\n\t"
+            "madc.lo.cc.u32 %6, %12, %9, %6;\n\t"
+            "madc.hi.cc.u32 %7, %12, %9, %7;\n\t"
+            "addc.u32 %8, %8, 0;"
+            : "+r"(y[0]), "+r"(y[1]), "+r"(y[2]), "+r"(y[3]), "+r"(y[4]), "+r"(y[5]), "+r"(y[6]), "+r"(y[7]), "+r"(c8)
+            : "r"(m), "r"(plimb<F, 2>()), "r"(plimb<F, 4>()), "r"(plimb<F, 6>()));
+        return;
+    }
+#endif
+    mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, c8);
+}
+
+// narrow window: the hi-aligned accumulator provably never carries out (see mont_mul)
+template <class F>
+PSD_DEV void redc_step(uint32_t* x, uint32_t* y) {
+    const uint32_t m = y[0] * np0<F>();
+    uint32_t unused = 0;
+    if (F::kBits == 255) redc_hi<F>(x, m, unused);
+    else mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    redc_lo<F>(y, m, x[7]);
+}
+
+// ------------------------------------------------------------------------------------------------
 // Field operations on fully reduced Montgomery residues in [0,p).
 // ------------------------------------------------------------------------------------------------
 
@@ -409,9 +474,7 @@ template <class F>
 PSD_DEV void mont_row(uint32_t* x, uint32_t* y, const uint32_t* a, uint32_t bi) {
     mad4_slide(x, y[0], a[1], a[3], a[5], a[7], bi);
     mad4(y, a[0], a[2], a[4], a[6], bi, x[7]);
-    const uint32_t m = y[0] * np0<F>();
-    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-    mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
+    redc_step<F>(x, y);
 }
 
 // r = a * b * 2^-256 mod p, fully reduced.  Requires a < 2^255 (true for any residue of either
@@ -424,9 +487,7 @@ PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     uint32_t e[8], o[8];
     mul4(e, a[0], a[2], a[4], a[6], b[0]);
     mul4(o, a[1], a[3], a[5], a[7], b[0]);
-    const uint32_t m = e[0] * np0<F>();
-    mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-    mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
+    redc_step<F>(o, e);
     mont_row<F>(e, o, a, b[1]);
     mont_row<F>(o, e, a, b[2]);
     mont_row<F>(e, o, a, b[3]);
@@ -457,9 +518,7 @@ PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8
         mad4(e, a[j][0], a[j][2], a[j][4], a[j][6], b[j][0], o[7]);
     }
     {
-        const uint32_t m = e[0] * np0<F>();
-        mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-        mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
+        redc_step<F>(o, e);
     }
     // rows 1..7: x = accumulator whose column 0 is now zero, y = the other one
 #pragma unroll
@@ -473,9 +532,7 @@ PSD_DEV void mont_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*b)[8
             mad4_nc(x, a[j][1], a[j][3], a[j][5], a[j][7], b[j][i]);
             mad4(y, a[j][0], a[j][2], a[j][4], a[j][6], b[j][i], x[7]);
         }
-        const uint32_t m = y[0] * np0<F>();
-        mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-        mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
+        redc_step<F>(x, y);
     }
     uint32_t s[8];
     merge8(s, e, o);        // after row 7: o[0] == 0
@@ -496,9 +553,7 @@ PSD_DEV void sqr_row(uint32_t* x, uint32_t* y, const uint32_t* v, uint32_t ai) {
     // odd-index entries ride the sliding (hi-aligned) chain, even-index entries the lo-aligned one
     mad4_slide_from<I / 2>(x, y[0], v[1], v[3], v[5], v[7], ai);
     mad4_from<(I + 1) / 2>(y, v[0], v[2], v[4], v[6], ai, x[7]);
-    const uint32_t m = y[0] * np0<F>();
-    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-    mad4(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7]);
+    redc_step<F>(x, y);
 }
 
 // r = a^2 * 2^-256 mod p with 36 wide multiplies for the product instead of 64: each off-diagonal
@@ -521,9 +576,7 @@ PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
         const uint32_t d1 = d[1] & 0xfffffffeu;
         mul4(e, a[0], d[2], d[4], d[6], a[0]);
         mul4(o, d1, d[3], d[5], d[7], a[0]);
-        const uint32_t m = e[0] * np0<F>();
-        mad4_nc(o, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-        mad4(e, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, o[7]);
+        redc_step<F>(o, e);
     }
     uint32_t v[8];
 #define PSD_SQR_ROW(I, X, Y)                                        \
@@ -585,8 +638,10 @@ PSD_DEV void mad4w_slide(uint32_t* x, uint32_t& y0, uint32_t a0, uint32_t a1, ui
 template <class F>
 PSD_DEV void redc_step_w(uint32_t* x, uint32_t* y, uint32_t& top) {
     const uint32_t m = y[0] * np0<F>();
-    mad4(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m, top);
-    mad4w_lo<0>(y, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, x[7], top);
+    redc_hi<F>(x, m, top);
+    uint32_t c = 0;
+    redc_lo<F>(y, m, c);
+    add_carry2(x[7], top, c);
 }
 // r = (w + (z >> 32) + top * 2^256) mod p for a value below 3p
 template <class F>
