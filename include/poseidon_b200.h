@@ -136,7 +136,9 @@ psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, 
 /* Merkle root over n_leaves (a power of two) with the 2-to-1 compression
  *   H(l, r) := { s = PoseidonSponge::new; s.absorb(&[l, r]); s.squeeze_native_field_elements(1)[0] }
  * (rate >= 2).  leaves: n_leaves elements (AoS); root: 1 element.  Intermediate levels live in a
- * device scratch buffer the call allocates and frees (n_leaves/2 + n_leaves/4 elements). */
+ * device scratch buffer (n_leaves/2 + n_leaves/4 elements) that the call allocates with cudaMalloc
+ * when it is missing or too small and the context keeps until it is destroyed; calls on one
+ * context are serialised.  The call returns when the root has been written. */
 psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root,
                            int repr, int mem, void* stream);
 /* One tree level only: out[i] = H(in[2i], in[2i+1]), i < n_pairs (device or host pointers). */
@@ -151,7 +153,8 @@ psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, 
  * hands every byte to its own arena cannot let a library call cudaMalloc afterwards -- the call can
  * fail outright (nothing is left outside the arena), it takes a process-wide driver lock that stalls
  * the other streams, and in such code bases an allocation on the request path is treated as a bug.
- * psd_merkle_root allocates and frees its level buffers on every call, so it is unusable there.
+ * psd_merkle_root allocates its level buffers with cudaMalloc whenever a tree is larger than any
+ * seen before on that context, so it is unusable there.
  *
  * This entry point computes the same root with the intermediate levels kept in a fixed scratch
  * array that is part of the library image: PSD_NOALLOC_MAX_LEAVES/2 + PSD_NOALLOC_MAX_LEAVES/4

@@ -145,6 +145,13 @@ struct psd_ctx {
     size_t stage_in_bytes = 0, stage_out_bytes = 0;
     int32_t* d_err = nullptr;
     int32_t* h_err = nullptr;   // pinned
+    // psd_merkle_root work space, kept between calls (cudaMalloc/cudaFree of hundreds of MB per call
+    // cost 5-25 ms and made the step time jitter); grown on demand, released with the context
+    std::mutex merkle_mu;
+    void* merkle_scratch = nullptr;
+    size_t merkle_scratch_bytes = 0;
+    void* merkle_leaves = nullptr;   // device copy of host leaves
+    size_t merkle_leaves_bytes = 0;
 };
 
 namespace {
@@ -590,6 +597,8 @@ static void ctx_teardown(psd_ctx* ctx) {
         }
         if (ctx->d_err) cudaFree(ctx->d_err);
         if (ctx->h_err) cudaFreeHost(ctx->h_err);
+        if (ctx->merkle_scratch) cudaFree(ctx->merkle_scratch);
+        if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
     }
     if (ctx->pool_held) pool_free(ctx->device, ctx->pool_off);
     delete ctx;
@@ -864,18 +873,31 @@ psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves
     }
     // scratch: [level 1: n/2][level 2: n/4] elements, ping-pong above that; Montgomery inside
     const size_t half = n_leaves / 2, quarter = std::max<size_t>(n_leaves / 4, 1);
-    uint32_t* scratch = nullptr;
-    uint32_t* d_leaves = nullptr;
-    PSD_CUDA(cudaMalloc(&scratch, (half + quarter) * 32));
+    std::lock_guard<std::mutex> lk(ctx->merkle_mu);
+    auto grow = [](void** buf, size_t* have, size_t need) -> bool {
+        if (need <= *have) return true;
+        if (*buf) cudaFree(*buf);
+        *buf = nullptr;
+        *have = 0;
+        if (cudaMalloc(buf, need) != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
+        *have = need;
+        return true;
+    };
+    if (!grow(&ctx->merkle_scratch, &ctx->merkle_scratch_bytes, (half + quarter) * 32))
+        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for Merkle levels failed", (half + quarter) * 32);
+    uint32_t* scratch = static_cast<uint32_t*>(ctx->merkle_scratch);
     psd_status result = PSD_OK;
     do {
         const uint32_t* src = as_u32(leaves);
         if (mem == PSD_MEM_HOST) {
-            if (cudaMalloc(&d_leaves, n_leaves * 32) != cudaSuccess) {
+            if (!grow(&ctx->merkle_leaves, &ctx->merkle_leaves_bytes, n_leaves * 32)) {
                 result = fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for leaves failed", n_leaves * 32);
-                cudaGetLastError();
                 break;
             }
+            uint32_t* d_leaves = static_cast<uint32_t*>(ctx->merkle_leaves);
             if (cudaMemcpyAsync(d_leaves, leaves, n_leaves * 32, cudaMemcpyHostToDevice, s) != cudaSuccess) {
                 result = fail(PSD_ERR_CUDA, "leaf upload failed: %s", cudaGetErrorString(cudaGetLastError()));
                 break;
@@ -912,8 +934,6 @@ psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves
         result = check_err_flag(ctx, s);
     } while (0);
     cudaStreamSynchronize(s);
-    cudaFree(scratch);
-    if (d_leaves) cudaFree(d_leaves);
     return result;
 }
 

@@ -38,7 +38,7 @@ def test_noalloc_merkle_root_matches_allocating_entry_point():
             ctx.synth_fill_dev(leaves.data_ptr(), n_leaves, seed, repr=repr_, stream=stream)
             want = torch.zeros((1, 4), dtype=torch.int64, device=dev)
             got = torch.zeros((1, 4), dtype=torch.int64, device=dev)
-            # existing entry point (allocates and frees its level buffers)
+            # existing entry point (allocates its level buffers with cudaMalloc)
             L.check(lib.psd_merkle_root(ctx.handle, leaves.data_ptr(), n_leaves, want.data_ptr(), repr_, L.MEM_DEVICE,
                                         stream))
             # new entry point: same inputs, caller-owned output, no allocation inside
