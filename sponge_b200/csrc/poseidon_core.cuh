@@ -141,6 +141,17 @@ PSD_DEV void dot_group(uint32_t* part, const uint32_t (*a)[8], const uint32_t (*
 template <class F, int T>
 PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
     // r = sum_{j<T} st[j] * c_pool[coeff_off + 8j ...], in groups of at most DotLimit<F>::kMax terms
+    if (T == 5 && F::kBits == 254) {
+        // BN254, five terms: one lazily reduced group on the wide window (6p > 2^256 rules out the
+        // 9-limb window; the result is < 1.95p, within reduce_3p's range) -- one reduction instead of two
+        uint32_t cf[T][8];
+#pragma unroll
+        for (int j = 0; j < T; j++)
+#pragma unroll
+            for (int k = 0; k < 8; k++) cf[j][k] = c_pool[coeff_off + j * 8 + k];
+        mont_dot_w<F, T>(r, st, cf);
+        return;
+    }
     constexpr int G = DotLimit<F>::kMax;
     bool first = true;
 #pragma unroll

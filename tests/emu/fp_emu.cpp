@@ -139,3 +139,9 @@ extern "C" void emu_mont_sqr_w(int field, uint32_t* r, const uint32_t* a, size_t
         else mont_sqr_w<Bls12381Fr>(r + 8 * i, a + 8 * i);
     }
 }
+
+extern "C" void emu_mont_dot_w5_bn254(uint32_t* r, const uint32_t* a, const uint32_t* b, size_t n) {
+    for (size_t i = 0; i < n; i++)
+        mont_dot_w<Bn254Fr, 5>(r + 8 * i, reinterpret_cast<const uint32_t(*)[8]>(a + i * 40),
+                               reinterpret_cast<const uint32_t(*)[8]>(b + i * 40));
+}
