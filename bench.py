@@ -206,6 +206,32 @@ class ClockSampler:
                     samples=len(sm), power_w_max=max(power) if power else None)
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Best effort: run this rank on the CPUs of the NUMA node its GPU hangs off, BEFORE pinned host
+    buffers are allocated (first touch then places them next to the GPU's PCIe root).  With 8 ranks
+    streaming 3 GiB per step each, cross-socket traffic otherwise limits the end-to-end number."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
@@ -251,6 +277,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product arm has no CPU path (use --impl reference)")
     torch.cuda.set_device(local_rank)
+    numa_node = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -389,7 +416,7 @@ def main():
         e2e = dict(value=units * world * e2e_steps / dt, unit="perm/s", h2d_bytes_per_step=in_el * 32,
                    d2h_bytes_per_step=out_el * 32, steps=e2e_steps,
                    note="psd_permute_batch/psd_absorb_squeeze_batch with PSD_MEM_HOST on pinned buffers; "
-                        "wall clock around blocking calls")
+                        "wall clock around blocking calls", numa_node=numa_node)
 
     if rank != 0:
         if dist is not None:

@@ -224,15 +224,16 @@ def test_device_pointer_path_with_torch_stream(S, pairs):
 
 def test_large_batch_properties(S, pairs):
     """Size-independent checks at a larger size through the staged host path (the library splits a
-    host batch into chunks of at most 2^20 sponges over three streams): sampled states against the
-    oracle, including both sides of the chunk boundary, and the permutation is a bijection on the
-    sample (distinct inputs -> distinct outputs)."""
+    host batch into chunks of 2^16 sponges over three streams): sampled states against the oracle,
+    including both sides of chunk boundaries, and the permutation is a bijection on the sample
+    (distinct inputs -> distinct outputs)."""
     pr = pairs("bn254_t3")
     n = (1 << 20) + 12345
     st = pr.orc.synth(n * 3, seed=0xF2)
     got = pr.ctx.permute_batch(st.copy()).reshape(n, 12)
     idx = np.unique(np.concatenate([np.arange(0, 4096), np.arange(n - 4096, n), np.arange(0, n, 257),
-                                    np.arange((1 << 20) - 64, (1 << 20) + 64)]))
+                                    np.arange((1 << 20) - 64, (1 << 20) + 64), np.arange((1 << 16) - 64, (1 << 16) + 64),
+                                    np.arange(3 * (1 << 16) - 64, 3 * (1 << 16) + 64)]))
     sample = st.reshape(n, 12)[idx].copy().reshape(-1, 4)
     exp = pr.orc.permute_batch(sample).reshape(-1, 12)
     assert np.array_equal(got[idx], exp)
@@ -246,7 +247,8 @@ def test_multi_chunk_soa_and_hash_host_path(S, pairs):
     n = (1 << 20) + 777
     st = pr.orc.synth(n * 3, seed=0xF3)
     got = unsoa(pr.ctx.permute_batch(soa(st, n, 3), layout=S.LAYOUT_SOA), n, 3).reshape(n, 12)
-    idx = np.unique(np.concatenate([np.arange(0, 512), np.arange(n - 512, n), np.arange((1 << 20) - 32, (1 << 20) + 32)]))
+    idx = np.unique(np.concatenate([np.arange(0, 512), np.arange(n - 512, n), np.arange((1 << 20) - 32, (1 << 20) + 32),
+                                    np.arange((1 << 16) - 32, (1 << 16) + 32), np.arange(5 * (1 << 16) - 32, 5 * (1 << 16) + 32)]))
     exp = pr.orc.permute_batch(st.reshape(n, 12)[idx].copy().reshape(-1, 4)).reshape(-1, 12)
     assert np.array_equal(got[idx], exp)
     x = st[: n * 2]
