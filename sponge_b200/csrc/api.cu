@@ -248,7 +248,8 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
 }
 
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
-    const int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
+    int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
+    if (variant >= 3 && !ctx->desc.ctab_ok) variant = 2;
     const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
@@ -535,6 +536,13 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     if (t <= 5)
         append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
 
+    // digit tables for constant products (variant 3): large, so only where a kernel uses them (t = 3)
+    // and only if the constant bank still has room -- otherwise the context runs variant 2
+    const size_t base_words = img.size();
+    const PermDesc base_desc = ctx->desc;
+    if (t == 3 && ctx->desc.opt_ok)
+        append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img);
+
     DeviceGuard guard(device);
     if (!guard.ok) {
         delete ctx;
@@ -542,8 +550,15 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     }
     ctx->pool_len = (uint32_t)img.size();
     if (!pool_alloc(device, ctx->pool_len, &ctx->pool_off)) {
-        delete ctx;
-        return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts", (unsigned)img.size());
+        if (img.size() > base_words) {   // retry without the digit tables
+            img.resize(base_words);
+            ctx->desc = base_desc;
+            ctx->pool_len = (uint32_t)img.size();
+        }
+        if (img.size() > base_words || !pool_alloc(device, ctx->pool_len, &ctx->pool_off)) {
+            delete ctx;
+            return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts", (unsigned)img.size());
+        }
     }
     ctx->pool_held = true;
     offset_desc(ctx->desc, ctx->pool_off);
@@ -623,7 +638,7 @@ psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
 
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
     if (!ctx) return fail(PSD_ERR_ARG, "null context");
-    if (variant < 0 || variant > 2) return fail(PSD_ERR_ARG, "variant must be 0, 1 or 2");
+    if (variant < 0 || variant > 3) return fail(PSD_ERR_ARG, "variant must be 0..3");
     ctx->variant = variant;
     return PSD_OK;
 }

@@ -775,6 +775,187 @@ PSD_DEV void mont_sqr_w(uint32_t* r, const uint32_t* a) {
     reduce_3p<F>(r, e, o, top);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Multiplication by CONSTANTS without a full Montgomery reduction ("digit tables").
+//
+// For a constant c the host precomputes  tab[d] = c * 2^(64 d) * 2^96 mod p  (d = 0..3, canonical).
+// For any a = sum_d D_d 2^(64 d) (64-bit digits D_d = (lo, hi) limbs):
+//     a * c * 2^96  ==  sum_d D_d * tab[d]   (mod p)
+// The right-hand side is 4 products of a 64-bit digit with a 256-bit table entry -- 64 wide
+// multiplies, all accumulated at FIXED alignment into an 11-limb accumulator (no per-row reduction, no
+// sliding) -- and the sum S < N * 2^66 * p of N such products needs only THREE Montgomery rows to
+// divide the 2^96 back out: S * 2^-96 + (<p*(1+2^-31)) < 2p.  So a constant product costs
+// 64 + 24 wide multiplies instead of 128, a sum of N constant products 64 N + 24 instead of 64 N + 64,
+// for ANY N and either field.  If `a` is a Montgomery residue, so is the result.
+//
+// Accumulator: e[10] = columns 0..9 (pairs at even columns), o[8] = columns 1..8 (pairs at odd
+// columns), top = column 10.
+// ------------------------------------------------------------------------------------------------
+// d[0..7] (four pairs) += {a0..a3} * b; the carry out ripples into r0, r1, top
+PSD_DEV void mad4_rip3(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b, uint32_t& r0,
+                       uint32_t& r1, uint32_t& top) {
+#if !defined(PSD_HOST_EMU)
+    asm("mad.lo.cc.u32 %0, %11, %15, %0;\n\t"
+        "madc.hi.cc.u32 %1, %11, %15, %1;\n\t"
+        "madc.lo.cc.u32 %2, %12, %15, %2;\n\t"
+        "madc.hi.cc.u32 %3, %12, %15, %3;\n\t"
+        "madc.lo.cc.u32 %4, %13, %15, %4;\n\t"
+        "madc.hi.cc.u32 %5, %13, %15, %5;\n\t"
+        "madc.lo.cc.u32 %6, %14, %15, %6;\n\t"
+        "madc.hi.cc.u32 %7, %14, %15, %7;\n\t"
+        "addc.cc.u32 %8, %8, 0;\n\t"
+        "addc.cc.u32 %9, %9, 0;\n\t"
+        "addc.u32 %10, %10, 0;"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7]), "+r"(r0),
+          "+r"(r1), "+r"(top)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    uint32_t c = 0;
+    mad4(d, a0, a1, a2, a3, b, c);
+    uint64_t s = (uint64_t)r0 + c;
+    r0 = (uint32_t)s;
+    s = (uint64_t)r1 + (s >> 32);
+    r1 = (uint32_t)s;
+    top += (uint32_t)(s >> 32);
+#endif
+}
+// same, carry ripples into r1, top
+PSD_DEV void mad4_rip2(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b, uint32_t& r1,
+                       uint32_t& top) {
+#if !defined(PSD_HOST_EMU)
+    asm("mad.lo.cc.u32 %0, %10, %14, %0;\n\t"
+        "madc.hi.cc.u32 %1, %10, %14, %1;\n\t"
+        "madc.lo.cc.u32 %2, %11, %14, %2;\n\t"
+        "madc.hi.cc.u32 %3, %11, %14, %3;\n\t"
+        "madc.lo.cc.u32 %4, %12, %14, %4;\n\t"
+        "madc.hi.cc.u32 %5, %12, %14, %5;\n\t"
+        "madc.lo.cc.u32 %6, %13, %14, %6;\n\t"
+        "madc.hi.cc.u32 %7, %13, %14, %7;\n\t"
+        "addc.cc.u32 %8, %8, 0;\n\t"
+        "addc.u32 %9, %9, 0;"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]), "+r"(d[4]), "+r"(d[5]), "+r"(d[6]), "+r"(d[7]), "+r"(r1),
+          "+r"(top)
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b));
+#else
+    uint32_t c = 0;
+    mad4(d, a0, a1, a2, a3, b, c);
+    uint64_t s = (uint64_t)r1 + c;
+    r1 = (uint32_t)s;
+    top += (uint32_t)(s >> 32);
+#endif
+}
+
+// acc += (lo + hi*2^32) * t[0..7]
+PSD_DEV void cacc_digit(uint32_t* e, uint32_t* o, uint32_t& top, uint32_t lo, uint32_t hi, const uint32_t* t) {
+    mad4_rip3(e, t[0], t[2], t[4], t[6], lo, e[8], e[9], top);   // columns (0,1)..(6,7)
+    mad4_rip2(o, t[1], t[3], t[5], t[7], lo, e[9], top);         // columns (1,2)..(7,8)
+    mad4_rip2(o, t[0], t[2], t[4], t[6], hi, e[9], top);         // columns (1,2)..(7,8)
+    mad4(e + 2, t[1], t[3], t[5], t[7], hi, top);                // columns (2,3)..(8,9)
+}
+
+// x7 += c; t9 += carry; t10 += carry
+PSD_DEV void add_carry3(uint32_t& x7, uint32_t& t9, uint32_t& t10, uint32_t c) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %0, %3;\n\taddc.cc.u32 %1, %1, 0;\n\taddc.u32 %2, %2, 0;" : "+r"(x7), "+r"(t9), "+r"(t10) : "r"(c));
+#else
+    uint64_t s = (uint64_t)x7 + c;
+    x7 = (uint32_t)s;
+    s = (uint64_t)t9 + (s >> 32);
+    t9 = (uint32_t)s;
+    t10 += (uint32_t)(s >> 32);
+#endif
+}
+
+// One Montgomery row on an 11-column value: hi = hi-aligned (columns 1..8), lo = lo-aligned (0..7),
+// t9/t10 = columns 9/10.  Afterwards lo[0] == 0.
+template <class F>
+PSD_DEV void redc11(uint32_t* hi, uint32_t* lo, uint32_t& t9, uint32_t& t10) {
+    const uint32_t m = lo[0] * np0<F>();
+    uint32_t c = 0;
+    redc_hi<F>(hi, m, c);
+    add_carry2(t9, t10, c);
+    c = 0;
+    redc_lo<F>(lo, m, c);
+    add_carry3(hi[7], t9, t10, c);
+}
+
+// The window moves down one column: x (lo-aligned, x[0] == 0) becomes the hi-aligned accumulator,
+// y0 is column 0 of the other one; columns 9/10 shift down with it.
+PSD_DEV void slide11(uint32_t* x, uint32_t& y0, uint32_t& t9, uint32_t& t10) {
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %8, %8, %1;\n\t"
+        "addc.cc.u32 %0, %2, 0;\n\t"
+        "addc.cc.u32 %1, %3, 0;\n\t"
+        "addc.cc.u32 %2, %4, 0;\n\t"
+        "addc.cc.u32 %3, %5, 0;\n\t"
+        "addc.cc.u32 %4, %6, 0;\n\t"
+        "addc.cc.u32 %5, %7, 0;\n\t"
+        "addc.cc.u32 %6, 0, 0;\n\t"
+        "addc.cc.u32 %7, %9, 0;\n\t"
+        "addc.u32 %9, %10, 0;"
+        : "+r"(x[0]), "+r"(x[1]), "+r"(x[2]), "+r"(x[3]), "+r"(x[4]), "+r"(x[5]), "+r"(x[6]), "+r"(x[7]), "+r"(y0),
+          "+r"(t9)
+        : "r"(t10));
+#else
+    uint64_t s = (uint64_t)y0 + x[1];
+    y0 = (uint32_t)s;
+    uint64_t c = s >> 32;
+    for (int k = 0; k < 6; k++) {
+        s = (uint64_t)x[k + 2] + c;
+        x[k] = (uint32_t)s;
+        c = s >> 32;
+    }
+    x[6] = (uint32_t)c;
+    x[7] = t9;
+    t9 = t10;
+#endif
+    t10 = 0;
+}
+
+// r = S * 2^-96 mod p for the accumulated sum S (< 2^70 * p), fully reduced.
+template <class F>
+PSD_DEV void cacc_finish(uint32_t* r, const uint32_t* e, const uint32_t* o, uint32_t top) {
+    uint32_t y[8], x[8], t9, t10;
+#pragma unroll
+    for (int k = 0; k < 8; k++) y[k] = e[k];
+#pragma unroll
+    for (int k = 0; k < 7; k++) x[k] = o[k];
+#if !defined(PSD_HOST_EMU)
+    asm("add.cc.u32 %0, %3, %4;\n\taddc.cc.u32 %1, %5, 0;\n\taddc.u32 %2, %6, 0;"
+        : "=r"(x[7]), "=r"(t9), "=r"(t10)
+        : "r"(o[7]), "r"(e[8]), "r"(e[9]), "r"(top));
+#else
+    {
+        uint64_t s = (uint64_t)o[7] + e[8];
+        x[7] = (uint32_t)s;
+        s = (uint64_t)e[9] + (s >> 32);
+        t9 = (uint32_t)s;
+        t10 = top + (uint32_t)(s >> 32);
+    }
+#endif
+    redc11<F>(x, y, t9, t10);      // row 1: y[0] -> 0
+    slide11(y, x[0], t9, t10);     // y becomes hi-aligned, x lo-aligned
+    redc11<F>(y, x, t9, t10);      // row 2: x[0] -> 0
+    slide11(x, y[0], t9, t10);     // x hi-aligned, y lo-aligned
+    redc11<F>(x, y, t9, t10);      // row 3: y[0] -> 0
+    reduce_3p<F>(r, x, y, t9);     // value = x + (y >> 32) + t9*2^256 < 2p
+}
+
+// r = sum_{j<N} a[j] * c_j  (Montgomery in -> Montgomery out), tab[j][d][8] = digit tables of c_j
+template <class F, int N>
+PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*tab)[4][8]) {
+    uint32_t e[10], o[8], top = 0;
+#pragma unroll
+    for (int k = 0; k < 10; k++) e[k] = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) o[k] = 0;
+#pragma unroll
+    for (int j = 0; j < N; j++)
+#pragma unroll
+        for (int d = 0; d < 4; d++) cacc_digit(e, o, top, a[j][2 * d], a[j][2 * d + 1], tab[j][d]);
+    cacc_finish<F>(r, e, o, top);
+}
+
 // Squaring entry point used by the S-box: dedicated squaring where its bound holds.
 template <class F>
 PSD_DEV void fp_sqr(uint32_t* r, const uint32_t* a) {

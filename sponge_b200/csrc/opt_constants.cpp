@@ -150,7 +150,70 @@ void append_optimised_constants(const HostField& f, uint32_t t, uint32_t full_ro
     d.opt_ok = 1;
 }
 
+namespace {
+
+// tab[dgt] = c * 2^(64 dgt + 96) mod p, canonical, for a Montgomery-form constant c
+void push_digit_table(const HostField& f, const Fe& c_mont, const Fe pow_mont[4], std::vector<uint32_t>& img) {
+    for (int dgt = 0; dgt < 4; dgt++) {
+        // (cR)(XR)/R = cXR -> from_mont -> cX
+        push_fe(img, hf_from_mont(f, hf_mul(f, c_mont, pow_mont[dgt])));
+    }
+}
+
+Fe fe_from_image(const std::vector<uint32_t>& img, uint32_t word_off) {
+    Fe x;
+    for (int k = 0; k < 4; k++) x.v[k] = (uint64_t)img[word_off + 2 * k] | ((uint64_t)img[word_off + 2 * k + 1] << 32);
+    return x;
+}
+
+}  // namespace
+
+void append_digit_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
+                         const std::vector<Fe>& mds, PermDesc& d, std::vector<uint32_t>& img) {
+    (void)full_rounds;
+    d.ctab_ok = 0;
+    d.ct_m00_off = d.ct_mds_off = d.ct_pre_off = d.ct_sparse_off = 0;
+    if (!d.opt_ok) return;
+    // Montgomery forms of 2^(64 dgt + 96) mod p, by doubling
+    Fe pow_mont[4];
+    {
+        Fe x = {{1, 0, 0, 0}};
+        int have = 0;
+        for (int dgt = 0; dgt < 4; dgt++) {
+            const int want = 64 * dgt + 96;
+            for (; have < want; have++) {
+                uint64_t c = hf_add_raw(x.v, x.v, x.v);
+                if (c || hf_cmp(x.v, f.p) >= 0) hf_sub_raw(x.v, x.v, f.p);
+            }
+            pow_mont[dgt] = hf_to_mont(f, x);
+        }
+    }
+    const uint32_t rp = partial_rounds, n = t - 1;
+    d.ct_m00_off = (uint32_t)img.size();
+    push_digit_table(f, mds[0], pow_mont, img);
+    d.ct_mds_off = (uint32_t)img.size();
+    for (uint32_t i = 0; i < t * t; i++) push_digit_table(f, mds[i], pow_mont, img);
+    if (rp) {
+        // M_pre and the sparse rows are re-read from the image written by append_optimised_constants
+        const uint32_t pre = d.pre_mds_off, sparse = d.sparse_off;
+        std::vector<Fe> pre_m(t * t);
+        for (uint32_t i = 0; i < t * t; i++) pre_m[i] = fe_from_image(img, pre + i * 8);
+        std::vector<Fe> wv((size_t)rp * 2 * n);
+        for (uint32_t r = 0; r < rp; r++)
+            for (uint32_t j = 0; j < 2 * n; j++) wv[(size_t)r * 2 * n + j] = fe_from_image(img, sparse + (r * 2 * t + 2 + j) * 8);
+        d.ct_pre_off = (uint32_t)img.size();
+        for (uint32_t i = 0; i < t * t; i++) push_digit_table(f, pre_m[i], pow_mont, img);
+        d.ct_sparse_off = (uint32_t)img.size();
+        for (const Fe& c : wv) push_digit_table(f, c, pow_mont, img);
+    }
+    d.ctab_ok = 1;
+}
+
 void offset_desc(PermDesc& d, uint32_t pool_off) {
+    d.ct_m00_off += pool_off;
+    d.ct_mds_off += pool_off;
+    d.ct_pre_off += pool_off;
+    d.ct_sparse_off += pool_off;
     d.ark_off += pool_off;
     d.mds_off += pool_off;
     d.one_off += pool_off;

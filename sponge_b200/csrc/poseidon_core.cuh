@@ -38,6 +38,13 @@ struct PermDesc {
     uint32_t pre_mds_off;   // [T][T][8]  matrix of the last full round before the partial rounds
     uint32_t sparse_off;    // [partial][2T][8]: k, M00, w_1..w_{T-1}, v_1..v_{T-1} per partial round
     uint32_t post_ark_off;  // [T][8]     round constants of the first full round after the partial rounds
+    // digit tables for constant products (fp256.cuh const_dot); valid when ctab_ok != 0.  One table =
+    // 4 entries x 8 words.
+    uint32_t ctab_ok;
+    uint32_t ct_m00_off;    // [4][8]                table of mds[0][0]
+    uint32_t ct_mds_off;    // [T][T][4][8]          tables of the dense matrix
+    uint32_t ct_pre_off;    // [T][T][4][8]          tables of M_pre
+    uint32_t ct_sparse_off; // [partial][2(T-1)][4][8]: w_1..w_{T-1}, v_1..v_{T-1} per partial round
 };
 
 template <class F, int ALPHA>
@@ -328,6 +335,112 @@ PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
 #pragma unroll
                 for (int k = 0; k < 8; k++) v[k] = c_pool[sp + (T + 1 + j) * 8 + k];
                 mont_mul<F>(prod, st[0], v);
+                fp_add<F>(st[1], st[1], prod);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t t1 = st[1][k];
+#pragma unroll
+                    for (int l = 1; l + 1 < T; l++) st[l][k] = st[l + 1][k];
+                    st[T - 1][k] = t1;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) st[0][k] = nw[T - 1][k];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// VARIANT 3: the compact optimised permutation with every product by a round constant (matrix rows,
+// sparse-row coefficients, lane updates) done through digit tables (const_dot): 64 N + 24 wide
+// multiplies for an N-term row instead of 64 N + 64, and 88 instead of 128 for a lane update.  Only
+// the S-box keeps true Montgomery products.  Same results, bit for bit.
+// ------------------------------------------------------------------------------------------------
+// out = sum_j st[j] * c_j with the table of c_0 at off_first and those of c_1.. at off_rest + 32 (j-1)
+template <class F, int T>
+PSD_DEV void row_cdot(uint32_t* out, const uint32_t (*st)[8], uint32_t off_first, uint32_t off_rest) {
+    uint32_t tab[T][4][8];
+#pragma unroll
+    for (int j = 0; j < T; j++)
+#pragma unroll
+        for (int dgt = 0; dgt < 4; dgt++)
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                tab[j][dgt][k] = c_pool[(j == 0 ? off_first : off_rest + (j - 1) * 32) + dgt * 8 + k];
+    const_dot<F, T>(out, st, tab);
+}
+
+template <class F, int T, int ALPHA>
+PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
+    const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (uint32_t r = 0; r < d.total; r++) {
+        const bool full = (r < first_partial || r >= first_post);
+        const uint32_t sp = d.sparse_off + (r - first_partial) * (2 * T) * 8;                  // k lives here
+        const uint32_t spt = d.ct_sparse_off + (r - first_partial) * (2 * (T - 1)) * 32;       // w / v tables
+        const uint32_t ark = full ? ((r == first_post && d.partial) ? d.post_ark_off : d.ark_off + r * T * 8) : sp;
+        const uint32_t mat = (r + 1 == first_partial && d.partial) ? d.ct_pre_off : d.ct_mds_off;
+        const uint32_t n_iter = full ? T : 1;
+        // phase A: S-boxes
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (uint32_t i = 0; i < n_iter; i++) {
+            uint32_t c[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) c[k] = c_pool[ark + i * 8 + k];
+            fp_add<F>(st[0], st[0], c);
+            sbox_compact<F, ALPHA>(st[0], d);
+            if (full) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t t0 = st[0][k];
+#pragma unroll
+                    for (int l = 0; l + 1 < T; l++) st[l][k] = st[l + 1][k];
+                    st[T - 1][k] = t0;
+                }
+            }
+        }
+        // phase B: rows
+        uint32_t nw[T][8];
+#pragma unroll
+        for (int l = 0; l < T; l++)
+#pragma unroll
+            for (int k = 0; k < 8; k++) nw[l][k] = 0;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (uint32_t i = 0; i < n_iter; i++) {
+            const uint32_t off_first = full ? mat + i * T * 32 : d.ct_m00_off;
+            const uint32_t off_rest = full ? off_first + 32 : spt;
+            uint32_t t[8];
+            row_cdot<F, T>(t, st, off_first, off_rest);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+#pragma unroll
+                for (int l = 0; l + 1 < T; l++) nw[l][k] = nw[l + 1][k];
+                nw[T - 1][k] = t[k];
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int l = 0; l < T; l++)
+#pragma unroll
+                for (int k = 0; k < 8; k++) st[l][k] = nw[l][k];
+        } else {
+            // phase C: lane updates s_j += v_j * s0
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+            for (uint32_t j = 0; j + 1 < T; j++) {
+                uint32_t tab[1][4][8], prod[8];
+#pragma unroll
+                for (int dgt = 0; dgt < 4; dgt++)
+#pragma unroll
+                    for (int k = 0; k < 8; k++) tab[0][dgt][k] = c_pool[spt + (T - 1 + j) * 32 + dgt * 8 + k];
+                const_dot<F, 1>(prod, st, tab);
                 fp_add<F>(st[1], st[1], prod);
 #pragma unroll
                 for (int k = 0; k < 8; k++) {

@@ -41,9 +41,11 @@ PSD_REG(5, 1)
 PSD_REG(5, 2)
 #endif
 #if PSD_TU_T == 3
+PSD_REG(5, 3)
 PSD_REG(17, 0)
 PSD_REG(17, 1)
 PSD_REG(17, 2)
+PSD_REG(17, 3)
 #endif
 
 }  // namespace psd

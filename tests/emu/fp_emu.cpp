@@ -58,6 +58,7 @@ static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
         if (variant == 1 && d.opt_ok) permute_opt<F, T, ALPHA>(s, d);
         else if (variant == 2) permute_rolled<F, T, ALPHA>(s, d);
         else if (variant == 3 && d.opt_ok) permute_opt_compact<F, T, ALPHA>(s, d);
+        else if (variant == 4 && d.ctab_ok) permute_opt_ctab<F, T, ALPHA>(s, d);
         else permute_dense<F, T, ALPHA>(s, d);
         memcpy(st + i * T * 8, s, sizeof s);
     }
@@ -105,11 +106,13 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     d.half_full = rf / 2; d.partial = rp; d.total = rounds; d.rate = rate; d.capacity = capacity;
     d.alpha_lo = (uint32_t)alpha; d.alpha_hi = (uint32_t)(alpha >> 32);
     append_optimised_constants(*hf, t, rf, rp, ark, mds, d, img);
+    if (variant == 4) append_digit_tables(*hf, t, rf, rp, mds, d, img);
     if (img.size() > kConstPoolWords) return -2;
     memcpy(c_pool, img.data(), img.size() * 4);
     int rc = field == 0 ? emu_perm_f<Bn254Fr>(d, t, alpha, variant, states, n)
                         : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
     if (rc) return rc;
+    if (variant == 4 && !d.ctab_ok) return 1;
     return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }
 
@@ -144,4 +147,35 @@ extern "C" void emu_mont_dot_w5_bn254(uint32_t* r, const uint32_t* a, const uint
     for (size_t i = 0; i < n; i++)
         mont_dot_w<Bn254Fr, 5>(r + 8 * i, reinterpret_cast<const uint32_t(*)[8]>(a + i * 40),
                                reinterpret_cast<const uint32_t(*)[8]>(b + i * 40));
+}
+
+// digit-table constant products: tables built here with the host field (tab[d] = c * 2^(64d+96) mod p)
+static void build_digit_table(const HostField& hf, const uint32_t* c_mont, uint32_t (*tab)[8]) {
+    Fe c;
+    memcpy(c.v, c_mont, 32);
+    Fe canon = hf_from_mont(hf, c);
+    for (int d = 0; d < 4; d++) {
+        Fe pw = {{1, 0, 0, 0}};   // 2^(64d+96) mod p by doubling
+        for (int i = 0; i < 64 * d + 96; i++) {
+            uint64_t cy = hf_add_raw(pw.v, pw.v, pw.v);
+            if (cy || hf_cmp(pw.v, hf.p) >= 0) hf_sub_raw(pw.v, pw.v, hf.p);
+        }
+        Fe t = hf_from_mont(hf, hf_mul(hf, hf_to_mont(hf, canon), hf_to_mont(hf, pw)));
+        memcpy(tab[d], t.v, 32);
+    }
+}
+extern "C" void emu_const_dot(int field, int n_terms, uint32_t* r, const uint32_t* a, const uint32_t* c_mont, size_t n) {
+    const HostField* hf = host_field(field);
+    for (size_t i = 0; i < n; i++) {
+        uint32_t tab[4][4][8];
+        for (int j = 0; j < n_terms; j++) build_digit_table(*hf, c_mont + (i * n_terms + j) * 8, tab[j]);
+        const uint32_t(*ap)[8] = reinterpret_cast<const uint32_t(*)[8]>(a + i * n_terms * 8);
+#define PSD_CASE(N)                                                                  \
+    case N:                                                                          \
+        if (field == 0) const_dot<Bn254Fr, N>(r + 8 * i, ap, tab);                   \
+        else const_dot<Bls12381Fr, N>(r + 8 * i, ap, tab);                           \
+        break;
+        switch (n_terms) { PSD_CASE(1) PSD_CASE(2) PSD_CASE(3) PSD_CASE(4) }
+#undef PSD_CASE
+    }
 }

@@ -180,7 +180,10 @@ def test_permutation_variants_host_model(emu, ref, name):
     exp = orc.permute_batch(st.copy())
     ark = to_limbs(v for r in cfg.ark for v in r)
     mds = to_limbs(v for r in cfg.mds for v in r)
-    for variant in (0, 1, 2, 3):   # dense, optimised, rolled, compact optimised
+    variants = [0, 1, 2, 3]          # dense, optimised, rolled, compact optimised
+    if t <= 3:
+        variants.append(4)           # compact optimised with digit-table constant products
+    for variant in variants:
         s = st.copy().view(np.uint32)
         rc = emu.emu_permute(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
                              C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), variant,
