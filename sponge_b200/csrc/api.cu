@@ -49,15 +49,24 @@ static psd_status fail(psd_status s, const char* fmt, ...) {
 // ------------------------------------------------------------------------------------------------
 // Registries filled by static initialisers of the kernel translation units
 // ------------------------------------------------------------------------------------------------
-static std::vector<PoolUploadFn>& pool_uploaders() {
-    static std::vector<PoolUploadFn> v;
+struct PoolUploader {
+    int field, t;
+    PoolUploadFn fn;
+};
+static std::vector<PoolUploader>& pool_uploaders() {
+    static std::vector<PoolUploader> v;
     return v;
+}
+static PoolUploadFn find_uploader(int field, int t) {
+    for (const auto& u : pool_uploaders())
+        if (u.field == field && u.t == t) return u.fn;
+    return nullptr;
 }
 static std::vector<SpongeKernelEntry>& sponge_kernels() {
     static std::vector<SpongeKernelEntry> v;
     return v;
 }
-void register_pool_uploader(PoolUploadFn fn) { pool_uploaders().push_back(fn); }
+void register_pool_uploader(int field, int t, PoolUploadFn fn) { pool_uploaders().push_back(PoolUploader{field, t, fn}); }
 void register_sponge_kernel(const SpongeKernelEntry& e) { sponge_kernels().push_back(e); }
 
 static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, int variant) {
@@ -79,7 +88,9 @@ static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, in
 static std::atomic<uint64_t> g_launches{0};
 
 // ------------------------------------------------------------------------------------------------
-// Constant-bank slots: the 62 KiB pool is shared by the live contexts of a device.
+// Constant-bank slots: one 62 KiB pool per (device, field, t) -- the kernel unit's own c_pool --
+// shared by the live contexts of that kind.  The small-kernel unit keeps [R, R^2] of both fields at
+// fixed offsets (kMiscOne/kMiscR2), uploaded once per device.
 // ------------------------------------------------------------------------------------------------
 struct PoolSlot {
     uint32_t off, len;
@@ -88,11 +99,15 @@ struct DevicePool {
     std::mutex mu;
     std::vector<PoolSlot> used;   // sorted by off
 };
-static DevicePool g_pools[64];
+static DevicePool g_pools[64][2][10];
+static std::once_flag g_misc_once[64];
+static inline uint32_t misc_one_off(int field) { return (uint32_t)field * 16; }
+static inline uint32_t misc_r2_off(int field) { return (uint32_t)field * 16 + 8; }
 
-static bool pool_alloc(int device, uint32_t len, uint32_t* off) {
-    DevicePool& p = g_pools[device];
+static bool pool_alloc(int device, int field, int t, uint32_t len, uint32_t* off, bool* was_empty) {
+    DevicePool& p = g_pools[device][field][t];
     std::lock_guard<std::mutex> lk(p.mu);
+    if (was_empty) *was_empty = p.used.empty();
     uint32_t cur = 0;
     size_t pos = 0;
     for (; pos < p.used.size(); pos++) {
@@ -104,8 +119,13 @@ static bool pool_alloc(int device, uint32_t len, uint32_t* off) {
     *off = cur;
     return true;
 }
-static void pool_free(int device, uint32_t off) {
-    DevicePool& p = g_pools[device];
+static bool pool_is_empty(int device, int field, int t) {
+    DevicePool& p = g_pools[device][field][t];
+    std::lock_guard<std::mutex> lk(p.mu);
+    return p.used.empty();
+}
+static void pool_free(int device, int field, int t, uint32_t off) {
+    DevicePool& p = g_pools[device][field][t];
     std::lock_guard<std::mutex> lk(p.mu);
     for (size_t i = 0; i < p.used.size(); i++) {
         if (p.used[i].off == off) {
@@ -132,10 +152,11 @@ struct psd_ctx {
     uint32_t full_rounds = 0, partial_rounds = 0, rate = 0, capacity = 0, t = 0;
     uint64_t alpha = 0;
     std::vector<Fe> ark_mont, mds_mont;   // Montgomery copies of the parameters
-    PermDesc desc{};
+    PermDesc desc{};       // offsets into the sponge-kernel unit's pool
+    PermDesc misc_desc{};  // same parameters with one/r2 offsets of the small-kernel unit's pool
     uint32_t pool_off = 0, pool_len = 0;
     bool pool_held = false;
-    int variant = 2;
+    int variant = 3;   // falls back to 2 when the context has no digit tables
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;
@@ -216,25 +237,15 @@ int env_int(const char* name, int dflt) {
 }
 
 LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n) {
-    // One block per 128 sponges, scheduled by the hardware: measured 11% faster on B200 than a
-    // persistent grid-stride grid (blocks start staggered, so warps sit in different phases of the
-    // permutation and the multiplier pipe stays fed).  PSD_GRID_PER_SM=<k> (development knob) forces a
-    // grid-stride grid of k blocks per SM instead.
-    static const int grid_per_sm = env_int("PSD_GRID_PER_SM", 0);
+    // One 128-thread block per 128 sponges, scheduled by the hardware: measured 11% faster on B200
+    // than a persistent grid-stride grid (blocks start staggered, so warps sit in different phases of
+    // the permutation and the multiplier pipe stays fed), and the kernel has no per-thread loop so
+    // that ptxas keeps round constants on the uniform datapath.
+    (void)ctx;
+    (void)k;
     LaunchCfg cfg;
     cfg.block = 128;
-    const uint64_t need = (n + cfg.block - 1) / cfg.block;
-    if (grid_per_sm == 0) {
-        cfg.grid = (int)std::max<uint64_t>(1, std::min<uint64_t>(need, 0x7fffffffull));
-        return cfg;
-    }
-    int per_sm = grid_per_sm;
-    if (per_sm < 0 &&
-        (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k->fn, cfg.block, 0) != cudaSuccess ||
-         per_sm < 1))
-        per_sm = 1;
-    const uint64_t full = (uint64_t)ctx->sm_count * per_sm;
-    cfg.grid = (int)std::max<uint64_t>(1, std::min(full, need));
+    cfg.grid = (int)std::max<uint64_t>(1, (n + cfg.block - 1) / cfg.block);
     return cfg;
 }
 
@@ -253,6 +264,7 @@ psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
     const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
+    if (a.n > (uint64_t)0x7fffffff * 128) return fail(PSD_ERR_ARG, "batch too large for one launch (%llu sponges)", (unsigned long long)a.n);
     LaunchCfg cfg = sponge_cfg(ctx, k, a.n);
     k->fn<<<cfg.grid, cfg.block, 0, stream>>>(a);
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -536,11 +548,12 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     if (t <= 5)
         append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
 
-    // digit tables for constant products (variant 3): large, so only where a kernel uses them (t = 3)
-    // and only if the constant bank still has room -- otherwise the context runs variant 2
+    // Digit tables for constant products (variant 3) are large (about 8x the constants they cover), so a
+    // context gets them only where they are a measured win (BN254 Fr, t = 3) and only if it is the
+    // first live context of its (field, t) -- later ones run variant 2 and keep the bank free.
     const size_t base_words = img.size();
     const PermDesc base_desc = ctx->desc;
-    if (t == 3 && ctx->desc.opt_ok)
+    if (t == 3 && p->field == PSD_FIELD_BN254_FR && ctx->desc.opt_ok && pool_is_empty(device, p->field, (int)t))
         append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img);
 
     DeviceGuard guard(device);
@@ -549,15 +562,17 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
         return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", device);
     }
     ctx->pool_len = (uint32_t)img.size();
-    if (!pool_alloc(device, ctx->pool_len, &ctx->pool_off)) {
-        if (img.size() > base_words) {   // retry without the digit tables
+    if (!pool_alloc(device, p->field, (int)t, ctx->pool_len, &ctx->pool_off, nullptr)) {
+        const bool had_tables = img.size() > base_words;
+        if (had_tables) {   // retry without the digit tables
             img.resize(base_words);
             ctx->desc = base_desc;
             ctx->pool_len = (uint32_t)img.size();
         }
-        if (img.size() > base_words || !pool_alloc(device, ctx->pool_len, &ctx->pool_off)) {
+        if (!had_tables || !pool_alloc(device, p->field, (int)t, ctx->pool_len, &ctx->pool_off, nullptr)) {
             delete ctx;
-            return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts", (unsigned)img.size());
+            return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts of this field and width",
+                        (unsigned)img.size());
         }
     }
     ctx->pool_held = true;
@@ -581,7 +596,27 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     CTX_CUDA(cudaMemset(ctx->d_err, 0, sizeof(int32_t)));
     CTX_CUDA(cudaHostAlloc(&ctx->h_err, sizeof(int32_t), cudaHostAllocDefault));
     *ctx->h_err = 0;
-    for (PoolUploadFn up : pool_uploaders()) CTX_CUDA(up(ctx->pool_off, img.data(), (uint32_t)img.size(), nullptr));
+    {
+        PoolUploadFn up = find_uploader(ctx->field, (int)t);
+        if (!up) return cleanup(fail(PSD_ERR_UNSUPPORTED, "no kernels for field %d, t=%u in this build", ctx->field, t));
+        CTX_CUDA(up(ctx->pool_off, img.data(), (uint32_t)img.size(), nullptr));
+        // [R, R^2] of both fields for the small kernels (convert / synth), once per device
+        cudaError_t misc_err = cudaSuccess;
+        std::call_once(g_misc_once[device], [&] {
+            PoolUploadFn mu = find_uploader(-1, 0);
+            std::vector<uint32_t> m;
+            for (int fld = 0; fld < 2; fld++) {
+                const HostField* h = host_field(fld);
+                for (int k = 0; k < 4; k++) { m.push_back((uint32_t)h->one[k]); m.push_back((uint32_t)(h->one[k] >> 32)); }
+                for (int k = 0; k < 4; k++) { m.push_back((uint32_t)h->r2[k]); m.push_back((uint32_t)(h->r2[k] >> 32)); }
+            }
+            if (mu) misc_err = (cudaError_t)mu(0, m.data(), (uint32_t)m.size(), nullptr);
+        });
+        CTX_CUDA(misc_err);
+    }
+    ctx->misc_desc = ctx->desc;
+    ctx->misc_desc.one_off = misc_one_off(ctx->field);
+    ctx->misc_desc.r2_off = misc_r2_off(ctx->field);
     CTX_CUDA(cudaDeviceSynchronize());
 #undef CTX_CUDA
     if (!find_kernel(ctx->field, (int)t, ctx->alpha, ctx->variant))
@@ -618,7 +653,7 @@ static void ctx_teardown(psd_ctx* ctx) {
         if (ctx->merkle_scratch) cudaFree(ctx->merkle_scratch);
         if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
     }
-    if (ctx->pool_held) pool_free(ctx->device, ctx->pool_off);
+    if (ctx->pool_held) pool_free(ctx->device, ctx->field, (int)ctx->t, ctx->pool_off);
     delete ctx;
 }
 
@@ -705,7 +740,7 @@ static psd_status convert(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void
     if (n == 0) return PSD_OK;
     DeviceGuard guard(ctx->device);
     if (mem == PSD_MEM_DEVICE) {
-        PSD_CUDA(launch_convert(ctx->field, ctx->desc, as_u32(elems), n, to_m, ctx->d_err, misc_cfg(ctx, n), stream));
+        PSD_CUDA(launch_convert(ctx->field, ctx->misc_desc, as_u32(elems), n, to_m, ctx->d_err, misc_cfg(ctx, n), stream));
         g_launches++;
         return PSD_OK;
     }
@@ -718,7 +753,7 @@ static psd_status convert(psd_ctx* ctx, uint64_t* elems, size_t n, int mem, void
         const uint64_t cnt = std::min<uint64_t>(chunk, n - first);
         cudaStream_t s = ctx->streams[slot];
         PSD_CUDA(cudaMemcpyAsync(ctx->stage_in[slot], elems + first * 4, cnt * 32, cudaMemcpyHostToDevice, s));
-        PSD_CUDA(launch_convert(ctx->field, ctx->desc, (uint32_t*)ctx->stage_in[slot], cnt, to_m, ctx->d_err,
+        PSD_CUDA(launch_convert(ctx->field, ctx->misc_desc, (uint32_t*)ctx->stage_in[slot], cnt, to_m, ctx->d_err,
                                 misc_cfg(ctx, cnt), s));
         g_launches++;
         PSD_CUDA(cudaMemcpyAsync(elems + first * 4, ctx->stage_in[slot], cnt * 32, cudaMemcpyDeviceToHost, s));
@@ -739,7 +774,7 @@ psd_status psd_synth_fill(psd_ctx* ctx, uint64_t* dev_elems, size_t n, uint64_t 
     if (!valid_enum(repr, 1)) return fail(PSD_ERR_ARG, "bad repr");
     if (n == 0) return PSD_OK;
     DeviceGuard guard(ctx->device);
-    PSD_CUDA(launch_synth(ctx->field, ctx->desc, as_u32(dev_elems), n, seed, first_index, repr, misc_cfg(ctx, n), stream));
+    PSD_CUDA(launch_synth(ctx->field, ctx->misc_desc, as_u32(dev_elems), n, seed, first_index, repr, misc_cfg(ctx, n), stream));
     g_launches++;
     return PSD_OK;
 }

@@ -845,12 +845,14 @@ PSD_DEV void mad4_rip2(uint32_t* d, uint32_t a0, uint32_t a1, uint32_t a2, uint3
 #endif
 }
 
-// acc += (lo + hi*2^32) * t[0..7]
-PSD_DEV void cacc_digit(uint32_t* e, uint32_t* o, uint32_t& top, uint32_t lo, uint32_t hi, const uint32_t* t) {
-    mad4_rip3(e, t[0], t[2], t[4], t[6], lo, e[8], e[9], top);   // columns (0,1)..(6,7)
-    mad4_rip2(o, t[1], t[3], t[5], t[7], lo, e[9], top);         // columns (1,2)..(7,8)
-    mad4_rip2(o, t[0], t[2], t[4], t[6], hi, e[9], top);         // columns (1,2)..(7,8)
-    mad4(e + 2, t[1], t[3], t[5], t[7], hi, top);                // columns (2,3)..(8,9)
+// acc += (lo + hi*2^32) * t[0..7].  Carries out of the four chains are only COUNTED (c8, c9, c10 =
+// carries into columns 8, 9, 10); cacc_finish folds the counts in once.
+PSD_DEV void cacc_digit(uint32_t* e, uint32_t* o, uint32_t& c8, uint32_t& c9, uint32_t& c10, uint32_t lo, uint32_t hi,
+                        const uint32_t* t) {
+    mad4(e, t[0], t[2], t[4], t[6], lo, c8);        // columns (0,1)..(6,7)
+    mad4(o, t[1], t[3], t[5], t[7], lo, c9);        // columns (1,2)..(7,8)
+    mad4(o, t[0], t[2], t[4], t[6], hi, c9);        // columns (1,2)..(7,8)
+    mad4(e + 2, t[1], t[3], t[5], t[7], hi, c10);   // columns (2,3)..(8,9)
 }
 
 // x7 += c; t9 += carry; t10 += carry
@@ -914,23 +916,29 @@ PSD_DEV void slide11(uint32_t* x, uint32_t& y0, uint32_t& t9, uint32_t& t10) {
 
 // r = S * 2^-96 mod p for the accumulated sum S (< 2^70 * p), fully reduced.
 template <class F>
-PSD_DEV void cacc_finish(uint32_t* r, const uint32_t* e, const uint32_t* o, uint32_t top) {
+PSD_DEV void cacc_finish(uint32_t* r, const uint32_t* e, const uint32_t* o, uint32_t c8, uint32_t c9, uint32_t c10) {
     uint32_t y[8], x[8], t9, t10;
 #pragma unroll
     for (int k = 0; k < 8; k++) y[k] = e[k];
 #pragma unroll
     for (int k = 0; k < 7; k++) x[k] = o[k];
+    // column 8 = o[7] + e[8] + c8, column 9 = e[9] + c9 + carry, column 10 = c10 + carry
 #if !defined(PSD_HOST_EMU)
-    asm("add.cc.u32 %0, %3, %4;\n\taddc.cc.u32 %1, %5, 0;\n\taddc.u32 %2, %6, 0;"
-        : "=r"(x[7]), "=r"(t9), "=r"(t10)
-        : "r"(o[7]), "r"(e[8]), "r"(e[9]), "r"(top));
+    asm("add.cc.u32 %0, %3, %4;\n\t"
+        "addc.cc.u32 %1, %5, %7;\n\t"
+        "addc.u32 %2, %8, 0;\n\t"
+        "add.cc.u32 %0, %0, %6;\n\t"
+        "addc.cc.u32 %1, %1, 0;\n\t"
+        "addc.u32 %2, %2, 0;"
+        : "=&r"(x[7]), "=&r"(t9), "=&r"(t10)
+        : "r"(o[7]), "r"(e[8]), "r"(e[9]), "r"(c8), "r"(c9), "r"(c10));
 #else
     {
-        uint64_t s = (uint64_t)o[7] + e[8];
+        uint64_t s = (uint64_t)o[7] + e[8] + c8;
         x[7] = (uint32_t)s;
-        s = (uint64_t)e[9] + (s >> 32);
+        s = (uint64_t)e[9] + c9 + (s >> 32);
         t9 = (uint32_t)s;
-        t10 = top + (uint32_t)(s >> 32);
+        t10 = c10 + (uint32_t)(s >> 32);
     }
 #endif
     redc11<F>(x, y, t9, t10);      // row 1: y[0] -> 0
@@ -938,13 +946,17 @@ PSD_DEV void cacc_finish(uint32_t* r, const uint32_t* e, const uint32_t* o, uint
     redc11<F>(y, x, t9, t10);      // row 2: x[0] -> 0
     slide11(x, y[0], t9, t10);     // x hi-aligned, y lo-aligned
     redc11<F>(x, y, t9, t10);      // row 3: y[0] -> 0
-    reduce_3p<F>(r, x, y, t9);     // value = x + (y >> 32) + t9*2^256 < 2p
+    // value = x + (y >> 32) < 2p < 2^256 (columns 9 and 10 are empty again): one conditional subtraction
+    uint32_t s8[8];
+    merge8(s8, x, y);
+    cond_sub_p<F>(r, s8);
 }
 
-// r = sum_{j<N} a[j] * c_j  (Montgomery in -> Montgomery out), tab[j][d][8] = digit tables of c_j
-template <class F, int N>
-PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*tab)[4][8]) {
-    uint32_t e[10], o[8], top = 0;
+
+// r = sum_{j<N} a[j] * c_j  (Montgomery in -> Montgomery out); the table of c_j is `words(j, dgt, k)`
+template <class F, int N, class Words>
+PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], Words words) {
+    uint32_t e[10], o[8], c8 = 0, c9 = 0, c10 = 0;
 #pragma unroll
     for (int k = 0; k < 10; k++) e[k] = 0;
 #pragma unroll
@@ -952,8 +964,13 @@ PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], const uint32_t (*tab
 #pragma unroll
     for (int j = 0; j < N; j++)
 #pragma unroll
-        for (int d = 0; d < 4; d++) cacc_digit(e, o, top, a[j][2 * d], a[j][2 * d + 1], tab[j][d]);
-    cacc_finish<F>(r, e, o, top);
+        for (int d = 0; d < 4; d++) {
+            uint32_t t[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) t[k] = words(j, d, k);
+            cacc_digit(e, o, c8, c9, c10, a[j][2 * d], a[j][2 * d + 1], t);
+        }
+    cacc_finish<F>(r, e, o, c8, c9, c10);
 }
 
 // Squaring entry point used by the S-box: dedicated squaring where its bound holds.

@@ -180,6 +180,6 @@ static int misc_upload(uint32_t word_off, const uint32_t* words, uint32_t n_word
     return (int)cudaMemcpyToSymbolAsync(c_pool, words, (size_t)n_words * 4, (size_t)word_off * 4,
                                         cudaMemcpyHostToDevice, (cudaStream_t)stream);
 }
-static ConstPoolRegistrar g_misc_pool(misc_upload);
+static ConstPoolRegistrar g_misc_pool(-1, 0, misc_upload);
 
 }  // namespace psd

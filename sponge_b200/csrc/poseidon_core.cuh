@@ -359,15 +359,9 @@ PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
 // out = sum_j st[j] * c_j with the table of c_0 at off_first and those of c_1.. at off_rest + 32 (j-1)
 template <class F, int T>
 PSD_DEV void row_cdot(uint32_t* out, const uint32_t (*st)[8], uint32_t off_first, uint32_t off_rest) {
-    uint32_t tab[T][4][8];
-#pragma unroll
-    for (int j = 0; j < T; j++)
-#pragma unroll
-        for (int dgt = 0; dgt < 4; dgt++)
-#pragma unroll
-            for (int k = 0; k < 8; k++)
-                tab[j][dgt][k] = c_pool[(j == 0 ? off_first : off_rest + (j - 1) * 32) + dgt * 8 + k];
-    const_dot<F, T>(out, st, tab);
+    const_dot<F, T>(out, st, [=](int j, int dgt, int k) -> uint32_t {
+        return c_pool[(j == 0 ? off_first : off_rest + (j - 1) * 32) + dgt * 8 + k];
+    });
 }
 
 template <class F, int T, int ALPHA>
@@ -435,12 +429,9 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
 #pragma unroll 1
 #endif
             for (uint32_t j = 0; j + 1 < T; j++) {
-                uint32_t tab[1][4][8], prod[8];
-#pragma unroll
-                for (int dgt = 0; dgt < 4; dgt++)
-#pragma unroll
-                    for (int k = 0; k < 8; k++) tab[0][dgt][k] = c_pool[spt + (T - 1 + j) * 32 + dgt * 8 + k];
-                const_dot<F, 1>(prod, st, tab);
+                uint32_t prod[8];
+                const uint32_t voff = spt + (T - 1 + j) * 32;
+                const_dot<F, 1>(prod, st, [=](int, int dgt, int k) -> uint32_t { return c_pool[voff + dgt * 8 + k]; });
                 fp_add<F>(st[1], st[1], prod);
 #pragma unroll
                 for (int k = 0; k < 8; k++) {

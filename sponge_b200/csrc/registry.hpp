@@ -1,6 +1,8 @@
-// Every translation unit that holds kernels has its own copy of the constant bank image (c_pool is
-// a per-module __constant__ symbol) and registers (a) an uploader for it and (b) the sponge kernels
-// it instantiates.  api.cu walks these tables; nothing here is device code.
+// Every translation unit that holds kernels has its OWN 62 KiB constant pool (c_pool is a per-unit
+// __constant__ symbol) and registers (a) an uploader for it and (b) the sponge kernels it
+// instantiates.  A context's constants are uploaded only into the pool of the unit whose kernels it
+// runs, so parameter sets of different (field, t) never compete for constant-bank space.
+// api.cu walks these tables; nothing here is device code.
 #pragma once
 #include <stdint.h>
 
@@ -19,11 +21,12 @@ struct SpongeKernelEntry {
     const char* name;
 };
 
-void register_pool_uploader(PoolUploadFn fn);
+// field/t identify the translation unit's kernels; the small-kernel unit registers as (-1, 0)
+void register_pool_uploader(int field, int t, PoolUploadFn fn);
 void register_sponge_kernel(const SpongeKernelEntry& e);
 
 struct ConstPoolRegistrar {
-    explicit ConstPoolRegistrar(PoolUploadFn fn) { register_pool_uploader(fn); }
+    ConstPoolRegistrar(int field, int t, PoolUploadFn fn) { register_pool_uploader(field, t, fn); }
 };
 struct SpongeKernelRegistrar {
     explicit SpongeKernelRegistrar(const SpongeKernelEntry& e) { register_sponge_kernel(e); }

@@ -73,10 +73,15 @@ template <class F, int T, int ALPHA, int VARIANT>
 __global__ void __launch_bounds__(128, PSD_MIN_BLOCKS(T)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
     const PermDesc& d = a.d;
     const uint32_t rate = d.rate, cap = d.capacity;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     bool bad = false;
 
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+    // One sponge per thread and an early exit -- deliberately NOT a grid-stride loop: inside a
+    // (potentially divergent) per-thread loop ptxas stops using the uniform datapath, and every
+    // round-constant read turns from LDCU + uniform-register operand into LEA + LDC into a vector
+    // register (measured: +6 % instructions on the compact kernel, +10 % on the digit-table one).
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    {
         uint32_t st[T][8];
         if (a.state_in != nullptr) {
 #pragma unroll

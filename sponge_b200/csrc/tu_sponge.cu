@@ -24,7 +24,7 @@ static int tu_upload(uint32_t word_off, const uint32_t* words, uint32_t n_words,
     return (int)cudaMemcpyToSymbolAsync(c_pool, words, (size_t)n_words * 4, (size_t)word_off * 4,
                                         cudaMemcpyHostToDevice, (cudaStream_t)stream);
 }
-static ConstPoolRegistrar g_pool(tu_upload);
+static ConstPoolRegistrar g_pool(TuField::kFieldId, PSD_TU_T, tu_upload);
 
 #define PSD_REG(ALPHA, VARIANT)                                                                       \
     static SpongeKernelRegistrar g_reg_##ALPHA##_##VARIANT(SpongeKernelEntry{                         \

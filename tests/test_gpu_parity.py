@@ -92,9 +92,8 @@ def test_permute_dense_variant_equals_optimised(S, pairs, name):
     opt = pr.ctx.permute_batch(st.copy())
     pr.ctx.set_variant(2)
     compact = pr.ctx.permute_batch(st.copy())
-    pr.ctx.set_variant(3)          # digit tables (falls back to 2 where the context has none)
+    pr.ctx.set_variant(3)          # digit tables (falls back to 2 where the context has none); the default
     ctab = pr.ctx.permute_batch(st.copy())
-    pr.ctx.set_variant(2)
     assert np.array_equal(dense, opt)
     assert np.array_equal(dense, compact)
     assert np.array_equal(dense, ctab)
