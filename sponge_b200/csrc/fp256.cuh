@@ -953,9 +953,10 @@ PSD_DEV void cacc_finish(uint32_t* r, const uint32_t* e, const uint32_t* o, uint
 }
 
 
-// r = sum_{j<N} a[j] * c_j  (Montgomery in -> Montgomery out); the table of c_j is `words(j, dgt, k)`
-template <class F, int N, class Words>
-PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], Words words) {
+// r = sum_{j<N} a[j] * c_j  (Montgomery in -> Montgomery out); `entry(j, dgt, t)` fills t[0..7] with
+// entry dgt of the table of c_j (read where it is used, so only one entry is live at a time)
+template <class F, int N, class Entry>
+PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], Entry entry) {
     uint32_t e[10], o[8], c8 = 0, c9 = 0, c10 = 0;
 #pragma unroll
     for (int k = 0; k < 10; k++) e[k] = 0;
@@ -966,8 +967,7 @@ PSD_DEV void const_dot(uint32_t* r, const uint32_t (*a)[8], Words words) {
 #pragma unroll
         for (int d = 0; d < 4; d++) {
             uint32_t t[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) t[k] = words(j, d, k);
+            entry(j, d, t);
             cacc_digit(e, o, c8, c9, c10, a[j][2 * d], a[j][2 * d + 1], t);
         }
     cacc_finish<F>(r, e, o, c8, c9, c10);

@@ -16,10 +16,23 @@ namespace psd {
 constexpr uint32_t kConstPoolWords = 15872;
 
 #if defined(__CUDACC__)
-__constant__ uint32_t c_pool[kConstPoolWords];
+__constant__ __align__(16) uint32_t c_pool[kConstPoolWords];
 #else
 static uint32_t c_pool[kConstPoolWords];
 #endif
+
+// One field element (8 words) from the pool.  Offsets are multiples of 8 words, so this is two
+// 128-bit uniform loads (LDCU.128) with one address computation instead of eight 32-bit ones.
+PSD_DEV void cload8(uint32_t* dst, uint32_t off) {
+#if defined(__CUDACC__)
+    const uint4 lo = *reinterpret_cast<const uint4*>(&c_pool[off]);
+    const uint4 hi = *reinterpret_cast<const uint4*>(&c_pool[off + 4]);
+    dst[0] = lo.x; dst[1] = lo.y; dst[2] = lo.z; dst[3] = lo.w;
+    dst[4] = hi.x; dst[5] = hi.y; dst[6] = hi.z; dst[7] = hi.w;
+#else
+    for (int k = 0; k < 8; k++) dst[k] = c_pool[off + k];
+#endif
+}
 
 // What a kernel needs to know about one parameter set.  Offsets are in 32-bit words into c_pool.
 struct PermDesc {
@@ -61,8 +74,7 @@ PSD_DEV void sbox(uint32_t* x, const PermDesc& d) {
     } else {
         const uint64_t alpha = ((uint64_t)d.alpha_hi << 32) | d.alpha_lo;
         uint32_t one[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) one[k] = c_pool[d.one_off + k];
+        cload8(one, d.one_off);
         fp_pow_u64<F>(x, x, alpha, one);
     }
 }
@@ -74,8 +86,7 @@ PSD_DEV void round_dense(uint32_t (&st)[T][8], const PermDesc& d, uint32_t r, bo
 #pragma unroll
     for (int i = 0; i < T; i++) {
         uint32_t c[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) c[k] = c_pool[d.ark_off + (r * T + i) * 8 + k];
+        cload8(c, d.ark_off + (r * T + i) * 8);
         fp_add<F>(st[i], st[i], c);
     }
     // apply_s_box
@@ -92,8 +103,7 @@ PSD_DEV void round_dense(uint32_t (&st)[T][8], const PermDesc& d, uint32_t r, bo
 #pragma unroll
         for (int j = 0; j < T; j++) {
             uint32_t m[8], prod[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) m[k] = c_pool[d.mds_off + (i * T + j) * 8 + k];
+            cload8(m, d.mds_off + (i * T + j) * 8);
             mont_mul<F>(prod, st[j], m);
             if (j == 0) {
 #pragma unroll
@@ -154,8 +164,7 @@ PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
         uint32_t cf[T][8];
 #pragma unroll
         for (int j = 0; j < T; j++)
-#pragma unroll
-            for (int k = 0; k < 8; k++) cf[j][k] = c_pool[coeff_off + j * 8 + k];
+            cload8(cf[j], coeff_off + j * 8);
         mont_dot_w<F, T>(r, st, cf);
         return;
     }
@@ -166,9 +175,14 @@ PSD_DEV void row_dot(uint32_t* r, const uint32_t (*st)[8], uint32_t coeff_off) {
         uint32_t part[8];
         uint32_t cf[G][8];
 #pragma unroll
-        for (int j = 0; j < G; j++)
+        for (int j = 0; j < G; j++) {
+            if (j0 + j < T) {
+                cload8(cf[j], coeff_off + (j0 + j) * 8);
+            } else {
 #pragma unroll
-            for (int k = 0; k < 8; k++) cf[j][k] = (j0 + j < T) ? c_pool[coeff_off + (j0 + j) * 8 + k] : 0u;
+                for (int k = 0; k < 8; k++) cf[j][k] = 0u;
+            }
+        }
         const int n = (T - j0 < G) ? (T - j0) : G;
         dot_group<F, G>(part, st + j0, cf, n);
         if (first) {
@@ -186,8 +200,7 @@ PSD_DEV void full_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t ar
 #pragma unroll
     for (int i = 0; i < T; i++) {
         uint32_t c[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) c[k] = c_pool[ark_off + i * 8 + k];
+        cload8(c, ark_off + i * 8);
         fp_add<F>(st[i], st[i], c);
         sbox<F, ALPHA>(st[i], d);
     }
@@ -205,8 +218,7 @@ PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t
     // off -> [k][M00][w_1..w_{T-1}][v_1..v_{T-1}]
     {
         uint32_t c[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) c[k] = c_pool[off + k];
+        cload8(c, off);
         fp_add<F>(st[0], st[0], c);
         sbox<F, ALPHA>(st[0], d);
     }
@@ -217,8 +229,7 @@ PSD_DEV void partial_round_opt(uint32_t (&st)[T][8], const PermDesc& d, uint32_t
 #pragma unroll
     for (int j = 1; j < T; j++) {
         uint32_t v[8], prod[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = c_pool[off + (T + j) * 8 + k];
+        cload8(v, off + (T + j) * 8);
         mont_mul<F>(prod, st[0], v);
         fp_add<F>(st[j], st[j], prod);
     }
@@ -287,8 +298,7 @@ PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
         for (uint32_t i = 0; i < n_iter; i++) {
             uint32_t c[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) c[k] = c_pool[ark + i * 8 + k];
+            cload8(c, ark + i * 8);
             fp_add<F>(st[0], st[0], c);
             sbox_compact<F, ALPHA>(st[0], d);
             if (full) {   // rotate left: the next lane moves into position 0
@@ -332,8 +342,7 @@ PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
             for (uint32_t j = 0; j + 1 < T; j++) {
                 uint32_t v[8], prod[8];
-#pragma unroll
-                for (int k = 0; k < 8; k++) v[k] = c_pool[sp + (T + 1 + j) * 8 + k];
+                cload8(v, sp + (T + 1 + j) * 8);
                 mont_mul<F>(prod, st[0], v);
                 fp_add<F>(st[1], st[1], prod);
 #pragma unroll
@@ -359,8 +368,8 @@ PSD_DEV void permute_opt_compact(uint32_t (&st)[T][8], const PermDesc& d) {
 // out = sum_j st[j] * c_j with the table of c_0 at off_first and those of c_1.. at off_rest + 32 (j-1)
 template <class F, int T>
 PSD_DEV void row_cdot(uint32_t* out, const uint32_t (*st)[8], uint32_t off_first, uint32_t off_rest) {
-    const_dot<F, T>(out, st, [=](int j, int dgt, int k) -> uint32_t {
-        return c_pool[(j == 0 ? off_first : off_rest + (j - 1) * 32) + dgt * 8 + k];
+    const_dot<F, T>(out, st, [=](int j, int dgt, uint32_t* t) {
+        cload8(t, (j == 0 ? off_first : off_rest + (j - 1) * 32) + dgt * 8);
     });
 }
 
@@ -383,8 +392,7 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
         for (uint32_t i = 0; i < n_iter; i++) {
             uint32_t c[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) c[k] = c_pool[ark + i * 8 + k];
+            cload8(c, ark + i * 8);
             fp_add<F>(st[0], st[0], c);
             sbox_compact<F, ALPHA>(st[0], d);
             if (full) {
@@ -431,7 +439,7 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
             for (uint32_t j = 0; j + 1 < T; j++) {
                 uint32_t prod[8];
                 const uint32_t voff = spt + (T - 1 + j) * 32;
-                const_dot<F, 1>(prod, st, [=](int, int dgt, int k) -> uint32_t { return c_pool[voff + dgt * 8 + k]; });
+                const_dot<F, 1>(prod, st, [=](int, int dgt, uint32_t* t) { cload8(t, voff + dgt * 8); });
                 fp_add<F>(st[1], st[1], prod);
 #pragma unroll
                 for (int k = 0; k < 8; k++) {
@@ -462,8 +470,7 @@ PSD_DEV void permute_rolled(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
         for (int i = 0; i < T; i++) {
             uint32_t c[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) c[k] = c_pool[d.ark_off + (r * T + i) * 8 + k];
+            cload8(c, d.ark_off + (r * T + i) * 8);
             fp_add<F>(st[i], st[i], c);
         }
         const int n_sbox = full ? T : 1;
@@ -482,8 +489,7 @@ PSD_DEV void permute_rolled(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
             for (int j = 0; j < T; j++) {
                 uint32_t m[8], prod[8];
-#pragma unroll
-                for (int k = 0; k < 8; k++) m[k] = c_pool[d.mds_off + (i * T + j) * 8 + k];
+                cload8(m, d.mds_off + (i * T + j) * 8);
                 mont_mul<F>(prod, st[j], m);
                 fp_add<F>(acc, acc, prod);
             }
@@ -503,8 +509,7 @@ PSD_DEV void permute_rolled(uint32_t (&st)[T][8], const PermDesc& d) {
 template <class F>
 PSD_DEV void to_mont(uint32_t* x, const PermDesc& d) {
     uint32_t r2[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) r2[k] = c_pool[d.r2_off + k];
+    cload8(r2, d.r2_off);
     mont_mul<F>(x, x, r2);
 }
 template <class F>

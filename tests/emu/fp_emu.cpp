@@ -172,8 +172,8 @@ extern "C" void emu_const_dot(int field, int n_terms, uint32_t* r, const uint32_
         const uint32_t(*ap)[8] = reinterpret_cast<const uint32_t(*)[8]>(a + i * n_terms * 8);
 #define PSD_CASE(N)                                                                  \
     case N:                                                                          \
-        if (field == 0) const_dot<Bn254Fr, N>(r + 8 * i, ap, [&](int j, int d, int k) { return tab[j][d][k]; });    \
-        else const_dot<Bls12381Fr, N>(r + 8 * i, ap, [&](int j, int d, int k) { return tab[j][d][k]; });            \
+        if (field == 0) const_dot<Bn254Fr, N>(r + 8 * i, ap, [&](int j, int d, uint32_t* t) { memcpy(t, tab[j][d], 32); });    \
+        else const_dot<Bls12381Fr, N>(r + 8 * i, ap, [&](int j, int d, uint32_t* t) { memcpy(t, tab[j][d], 32); });            \
         break;
         switch (n_terms) { PSD_CASE(1) PSD_CASE(2) PSD_CASE(3) PSD_CASE(4) }
 #undef PSD_CASE
