@@ -247,7 +247,7 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 2 = optimised, compact rolled phases,
  * 3 = 2 + products by round constants through digit tables (default).  The tables take about 33 KB
  *     of the 62 KB constant pool that the contexts of one (field, width) share, so only the first
- *     live BN254 t=3 context gets them; every other context silently runs variant 2. */
+ *     live t=3 context of each field gets them; every other context silently runs variant 2. */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
 
 #ifdef __cplusplus
