@@ -260,7 +260,7 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
 
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
     int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
-    if (variant >= 3 && !ctx->desc.ctab_ok) variant = 2;
+    if (variant >= 3) variant = ctx->desc.ctab_ok == 1 ? 3 : ctx->desc.ctab_ok == 2 ? 4 : 2;
     const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
@@ -553,8 +553,12 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     // is the first live context of its (field, t) -- later ones run variant 2 and keep the bank free.
     const size_t base_words = img.size();
     const PermDesc base_desc = ctx->desc;
-    if (t == 3 && ctx->desc.opt_ok && pool_is_empty(device, p->field, (int)t))
-        append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img);
+    if (ctx->desc.opt_ok && pool_is_empty(device, p->field, (int)t)) {
+        if (t == 3)
+            append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img);
+        else if (t == 5 && p->alpha == 5)   // the full set does not fit at t = 5: lane-update tables only
+            append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img, true);
+    }
 
     DeviceGuard guard(device);
     if (!guard.ok) {

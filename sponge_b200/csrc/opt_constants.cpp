@@ -169,7 +169,7 @@ Fe fe_from_image(const std::vector<uint32_t>& img, uint32_t word_off) {
 }  // namespace
 
 void append_digit_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
-                         const std::vector<Fe>& mds, PermDesc& d, std::vector<uint32_t>& img) {
+                         const std::vector<Fe>& mds, PermDesc& d, std::vector<uint32_t>& img, bool lanes_only) {
     (void)full_rounds;
     d.ctab_ok = 0;
     d.ct_m00_off = d.ct_mds_off = d.ct_pre_off = d.ct_sparse_off = 0;
@@ -189,6 +189,17 @@ void append_digit_tables(const HostField& f, uint32_t t, uint32_t full_rounds, u
         }
     }
     const uint32_t rp = partial_rounds, n = t - 1;
+    if (lanes_only) {
+        if (!rp) return;
+        const uint32_t sparse = d.sparse_off;
+        std::vector<Fe> vs((size_t)rp * n);
+        for (uint32_t r = 0; r < rp; r++)
+            for (uint32_t j = 0; j < n; j++) vs[(size_t)r * n + j] = fe_from_image(img, sparse + (r * 2 * t + 2 + n + j) * 8);
+        d.ct_sparse_off = (uint32_t)img.size();
+        for (const Fe& c : vs) push_digit_table(f, c, pow_mont, img);
+        d.ctab_ok = 2;
+        return;
+    }
     d.ct_m00_off = (uint32_t)img.size();
     push_digit_table(f, mds[0], pow_mont, img);
     d.ct_mds_off = (uint32_t)img.size();

@@ -53,7 +53,7 @@ struct PermDesc {
     uint32_t post_ark_off;  // [T][8]     round constants of the first full round after the partial rounds
     // digit tables for constant products (fp256.cuh const_dot); valid when ctab_ok != 0.  One table =
     // 4 entries x 8 words.
-    uint32_t ctab_ok;
+    uint32_t ctab_ok;       // 0 = none, 1 = all tables, 2 = lane-update tables only (ct_sparse_off: [partial][T-1][4][8])
     uint32_t ct_m00_off;    // [4][8]                table of mds[0][0]
     uint32_t ct_mds_off;    // [T][T][4][8]          tables of the dense matrix
     uint32_t ct_pre_off;    // [T][T][4][8]          tables of M_pre
@@ -373,7 +373,9 @@ PSD_DEV void row_cdot(uint32_t* out, const uint32_t (*st)[8], uint32_t off_first
     });
 }
 
-template <class F, int T, int ALPHA>
+// LANES_ONLY: only the lane updates go through digit tables (for widths whose full table set does not
+// fit the constant pool, e.g. t = 5); rows stay lazily reduced Montgomery dot products as in variant 2.
+template <class F, int T, int ALPHA, bool LANES_ONLY = false>
 PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
     const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
 #if defined(__CUDACC__)
@@ -382,9 +384,11 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
     for (uint32_t r = 0; r < d.total; r++) {
         const bool full = (r < first_partial || r >= first_post);
         const uint32_t sp = d.sparse_off + (r - first_partial) * (2 * T) * 8;                  // k lives here
-        const uint32_t spt = d.ct_sparse_off + (r - first_partial) * (2 * (T - 1)) * 32;       // w / v tables
+        // w / v tables (LANES_ONLY: v tables only)
+        const uint32_t spt = d.ct_sparse_off + (r - first_partial) * ((LANES_ONLY ? 1 : 2) * (T - 1)) * 32;
         const uint32_t ark = full ? ((r == first_post && d.partial) ? d.post_ark_off : d.ark_off + r * T * 8) : sp;
-        const uint32_t mat = (r + 1 == first_partial && d.partial) ? d.ct_pre_off : d.ct_mds_off;
+        const uint32_t mat = LANES_ONLY ? ((r + 1 == first_partial && d.partial) ? d.pre_mds_off : d.mds_off)
+                                        : ((r + 1 == first_partial && d.partial) ? d.ct_pre_off : d.ct_mds_off);
         const uint32_t n_iter = full ? T : 1;
         // phase A: S-boxes
 #if defined(__CUDACC__)
@@ -415,10 +419,14 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
 #pragma unroll 1
 #endif
         for (uint32_t i = 0; i < n_iter; i++) {
-            const uint32_t off_first = full ? mat + i * T * 32 : d.ct_m00_off;
-            const uint32_t off_rest = full ? off_first + 32 : spt;
             uint32_t t[8];
-            row_cdot<F, T>(t, st, off_first, off_rest);
+            if (LANES_ONLY) {
+                row_dot<F, T>(t, st, full ? mat + i * T * 8 : sp + 8);
+            } else {
+                const uint32_t off_first = full ? mat + i * T * 32 : d.ct_m00_off;
+                const uint32_t off_rest = full ? off_first + 32 : spt;
+                row_cdot<F, T>(t, st, off_first, off_rest);
+            }
 #pragma unroll
             for (int k = 0; k < 8; k++) {
 #pragma unroll
@@ -438,7 +446,7 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
 #endif
             for (uint32_t j = 0; j + 1 < T; j++) {
                 uint32_t prod[8];
-                const uint32_t voff = spt + (T - 1 + j) * 32;
+                const uint32_t voff = spt + ((LANES_ONLY ? 0 : T - 1) + j) * 32;
                 const_dot<F, 1>(prod, st, [=](int, int dgt, uint32_t* t) { cload8(t, voff + dgt * 8); });
                 fp_add<F>(st[1], st[1], prod);
 #pragma unroll

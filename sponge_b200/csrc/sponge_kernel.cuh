@@ -50,6 +50,8 @@ template <class F, int T, int ALPHA, int VARIANT>
 __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d) {
     if constexpr (T > 5) {
         permute_rolled<F, T, ALPHA>(st, d);
+    } else if constexpr (VARIANT == 4) {
+        permute_opt_ctab<F, T, ALPHA, true>(st, d);    // lane-update tables only (d.ctab_ok == 2)
     } else if constexpr (VARIANT == 3) {
         permute_opt_ctab<F, T, ALPHA>(st, d);   // the host only selects this kernel when d.ctab_ok
     } else if constexpr (VARIANT == 2) {

@@ -40,6 +40,9 @@ PSD_REG(5, 0)
 PSD_REG(5, 1)
 PSD_REG(5, 2)
 #endif
+#if PSD_TU_T == 5
+PSD_REG(5, 4)
+#endif
 #if PSD_TU_T == 3
 PSD_REG(5, 3)
 PSD_REG(17, 0)

@@ -58,7 +58,8 @@ static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
         if (variant == 1 && d.opt_ok) permute_opt<F, T, ALPHA>(s, d);
         else if (variant == 2) permute_rolled<F, T, ALPHA>(s, d);
         else if (variant == 3 && d.opt_ok) permute_opt_compact<F, T, ALPHA>(s, d);
-        else if (variant == 4 && d.ctab_ok) permute_opt_ctab<F, T, ALPHA>(s, d);
+        else if (variant == 4 && d.ctab_ok == 1) permute_opt_ctab<F, T, ALPHA>(s, d);
+        else if (variant == 5 && d.ctab_ok == 2) permute_opt_ctab<F, T, ALPHA, true>(s, d);
         else permute_dense<F, T, ALPHA>(s, d);
         memcpy(st + i * T * 8, s, sizeof s);
     }
@@ -107,12 +108,13 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     d.alpha_lo = (uint32_t)alpha; d.alpha_hi = (uint32_t)(alpha >> 32);
     append_optimised_constants(*hf, t, rf, rp, ark, mds, d, img);
     if (variant == 4) append_digit_tables(*hf, t, rf, rp, mds, d, img);
+    if (variant == 5) append_digit_tables(*hf, t, rf, rp, mds, d, img, true);
     if (img.size() > kConstPoolWords) return -2;
     memcpy(c_pool, img.data(), img.size() * 4);
     int rc = field == 0 ? emu_perm_f<Bn254Fr>(d, t, alpha, variant, states, n)
                         : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
     if (rc) return rc;
-    if (variant == 4 && !d.ctab_ok) return 1;
+    if ((variant == 4 && d.ctab_ok != 1) || (variant == 5 && d.ctab_ok != 2)) return 1;
     return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }
 

@@ -183,6 +183,8 @@ def test_permutation_variants_host_model(emu, ref, name):
     variants = [0, 1, 2, 3]          # dense, optimised, rolled, compact optimised
     if t <= 3:
         variants.append(4)           # compact optimised with digit-table constant products
+    if cfg.partial_rounds and cfg.full_rounds >= 2:
+        variants.append(5)           # ... with tables for the lane updates only (the t = 5 mode)
     for variant in variants:
         s = st.copy().view(np.uint32)
         rc = emu.emu_permute(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
