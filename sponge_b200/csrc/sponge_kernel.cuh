@@ -65,10 +65,11 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 
 // Resident 128-thread blocks per SM the register allocation is steered towards (the multiplier pipe
 // needs >= 4 warps per scheduler to stay busy; see profiles/).  Overridable for tuning runs.
-// Measured on B200 (bench c2/c3, min blocks 3..7): t=3 is flat within 2 % (125-128 M perm/s), t=5 is
-// best when ptxas is left alone (138 registers, no spills), so only t<=3 gets a hint.
+// Measured on B200: with round constants in uniform registers the t=3 kernels need only 72 vector
+// registers, and 7 resident blocks (7 warps per scheduler) are best: c2 147.1 M perm/s vs 145.0 M at 5,
+// 146.2 M at 8 (spills); c5 159.2 M vs 156.0 M.  t=5 is best when ptxas is left alone.
 #ifndef PSD_MIN_BLOCKS
-#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 5 : 0)   /* 0 = no hint */
+#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 7 : 0)   /* 0 = no hint */
 #endif
 
 template <class F, int T, int ALPHA, int VARIANT>
