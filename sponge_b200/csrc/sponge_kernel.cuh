@@ -69,7 +69,7 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // registers, and 7 resident blocks (7 warps per scheduler) are best: c2 147.1 M perm/s vs 145.0 M at 5,
 // 146.2 M at 8 (spills); c5 159.2 M vs 156.0 M.  t=5 is best when ptxas is left alone.
 #ifndef PSD_MIN_BLOCKS
-#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 7 : 0)   /* 0 = no hint */
+#define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 7 : (T) == 5 ? 5 : 0)   /* 0 = no hint; t=5: 83.8 M vs 83.0 M hash/s */
 #endif
 
 template <class F, int T, int ALPHA, int VARIANT>
