@@ -442,16 +442,16 @@ def main():
     # of that on B200 (k0.imad_wide_per_s), so a kernel that executes all W_alg multiplies as IMAD.WIDE
     # tops out near 0.45; the optimised kernel gets above that by executing fewer multiplies than W_alg.
     # DRAM bytes per launch from the committed ncu --set full capture of this exact workload
-    # (profiles/r1_c2_final_v6_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
-    traffic = 3.189e9 if (name == "c2" and log_n == 24) else None
+    # (profiles/r1_c2_final_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
+    traffic = 3.191e9 if (name == "c2" and log_n == 24) else None
     roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_lo / 1e9, unit="Gimul/s",
                     frac=achieved_imul / imad_lo, traffic=traffic,
                     w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
                     # executed multiplies and multiplier-pipe activity of the shipped kernel for this workload, from
-                    # the committed ncu capture (profiles/r1_c2_final_v6_summary.md); W_exec < W_alg because of
+                    # the committed ncu capture (profiles/r1_c2_final_summary.md); W_exec < W_alg because of
                     # sparse partial rounds, digit-table constant products and dedicated squaring
                     w_exec_imul_per_perm=(56625 if name == "c2" else None),
-                    fmaheavy_active_pct_ncu=(86.3 if name == "c2" else None),
+                    fmaheavy_active_pct_ncu=(87.5 if name == "c2" else None),
                     peak_source="K0 probe in this run: sustained 32-bit IMAD results/s on all SMs "
                                 "(integer-multiply pipe issue rate)",
                     k0=dict(imad_wide_per_s=imad_wide, imad_lo_per_s=imad_lo, mont_mul_per_s=modmul_rate,
