@@ -25,8 +25,10 @@ static uint32_t c_pool[kConstPoolWords];
 // 128-bit uniform loads (LDCU.128) with one address computation instead of eight 32-bit ones.
 PSD_DEV void cload8(uint32_t* dst, uint32_t off) {
 #if defined(__CUDACC__)
-    const uint4 lo = *reinterpret_cast<const uint4*>(&c_pool[off]);
-    const uint4 hi = *reinterpret_cast<const uint4*>(&c_pool[off + 4]);
+    // indexing in 16-byte units makes the alignment provable (off is a runtime multiple of 8 words)
+    const uint4* q = reinterpret_cast<const uint4*>(c_pool) + (off >> 2);
+    const uint4 lo = q[0];
+    const uint4 hi = q[1];
     dst[0] = lo.x; dst[1] = lo.y; dst[2] = lo.z; dst[3] = lo.w;
     dst[4] = hi.x; dst[5] = hi.y; dst[6] = hi.z; dst[7] = hi.w;
 #else
