@@ -443,7 +443,7 @@ def main():
     # tops out near 0.45; the optimised kernel gets above that by executing fewer multiplies than W_alg.
     # DRAM bytes per launch from the committed ncu --set full capture of this exact workload
     # (profiles/r1_c2_final_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
-    traffic = 3.191e9 if (name == "c2" and log_n == 24) else None
+    traffic = 3.195e9 if (name == "c2" and log_n == 24) else None
     roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_lo / 1e9, unit="Gimul/s",
                     frac=achieved_imul / imad_lo, traffic=traffic,
                     w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
@@ -451,7 +451,7 @@ def main():
                     # the committed ncu capture (profiles/r1_c2_final_summary.md); W_exec < W_alg because of
                     # sparse partial rounds, digit-table constant products and dedicated squaring
                     w_exec_imul_per_perm=(56625 if name == "c2" else None),
-                    fmaheavy_active_pct_ncu=(87.5 if name == "c2" else None),
+                    fmaheavy_active_pct_ncu=(89.5 if name == "c2" else None),
                     peak_source="K0 probe in this run: sustained 32-bit IMAD results/s on all SMs "
                                 "(integer-multiply pipe issue rate)",
                     k0=dict(imad_wide_per_s=imad_wide, imad_lo_per_s=imad_lo, mont_mul_per_s=modmul_rate,
