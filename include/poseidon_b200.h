@@ -141,6 +141,15 @@ psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, 
  * context are serialised.  The call returns when the root has been written. */
 psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root,
                            int repr, int mem, void* stream);
+/* The whole tree: like psd_merkle_root but every internal node is returned.  nodes receives
+ * n_leaves - 1 elements, bottom-up: the n_leaves/2 parents of the leaves first, then the n_leaves/4
+ * nodes above them, ..., the root last (node j of level k, k = 1 for the leaves' parents, is at
+ * element offset n_leaves - n_leaves/2^(k-1) + j).  n_leaves >= 2, a power of two. */
+psd_status psd_merkle_tree(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* nodes, int repr, int mem,
+                           void* stream);
+/* Authentication path of leaf `index` out of the arrays above (host pointers, pure indexing):
+ * path receives log2(n_leaves) elements, the sibling at every level from the leaf's own up. */
+psd_status psd_merkle_path(const uint64_t* leaves, const uint64_t* nodes, size_t n_leaves, size_t index, uint64_t* path);
 /* One tree level only: out[i] = H(in[2i], in[2i+1]), i < n_pairs (device or host pointers). */
 psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, uint64_t* out, int repr,
                               int mem, void* stream);

@@ -67,6 +67,8 @@ _PROTOS = {
     "psd_absorb_squeeze_batch": (_i, [_vp, _vp, _sz, _u32, _u32, _vp, _i, _i, _i, _vp]),
     "psd_absorb_squeeze_bytes_batch": (_i, [_vp, _vp, _sz, _u32, _u32, _vp, _i, _i, _i, _vp]),
     "psd_merkle_root": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
+    "psd_merkle_tree": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
+    "psd_merkle_path": (_i, [_vp, _vp, _sz, _sz, _vp]),
     "psd_compress_pairs": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
     "psd_merkle_root_noalloc": (_i, [_vp, _vp, _sz, _vp, _i, _vp]),
     "psd_batch_new": (_i, [_vp, _sz, _pp]),

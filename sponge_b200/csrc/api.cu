@@ -1407,6 +1407,83 @@ psd_status psd_sponge_set_state(psd_sponge* s, const uint64_t* state, int repr, 
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------
+// Full Merkle tree (all internal nodes) and authentication paths
+// ------------------------------------------------------------------------------------------------
+extern "C" psd_status psd_merkle_tree(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* nodes, int repr,
+                                      int mem, void* stream) {
+    psd_status st = check_batch_args(ctx, leaves, PSD_LAYOUT_AOS, repr, mem);
+    if (st != PSD_OK) return st;
+    if (!nodes) return fail(PSD_ERR_ARG, "null nodes buffer");
+    if (ctx->rate < 2) return fail(PSD_ERR_UNSUPPORTED, "2-to-1 compression needs rate >= 2");
+    if (n_leaves < 2 || (n_leaves & (n_leaves - 1))) return fail(PSD_ERR_ARG, "n_leaves must be a power of two >= 2");
+    DeviceGuard guard(ctx->device);
+    cudaStream_t s = mem == PSD_MEM_DEVICE ? (cudaStream_t)stream : ctx->streams[0];
+    const uint32_t* d_leaves = as_u32(leaves);
+    uint32_t* d_nodes = as_u32(nodes);
+    std::unique_lock<std::mutex> lk(ctx->merkle_mu, std::defer_lock);
+    if (mem == PSD_MEM_HOST) {
+        // stage through the context's Merkle buffers: [leaves | nodes]
+        lk.lock();
+        const size_t need = (2 * n_leaves - 1) * 32;
+        if (need > ctx->merkle_leaves_bytes) {
+            if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
+            ctx->merkle_leaves = nullptr;
+            ctx->merkle_leaves_bytes = 0;
+            if (cudaMalloc(&ctx->merkle_leaves, need) != cudaSuccess) {
+                cudaGetLastError();
+                return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for the tree failed", need);
+            }
+            ctx->merkle_leaves_bytes = need;
+        }
+        uint32_t* base = static_cast<uint32_t*>(ctx->merkle_leaves);
+        PSD_CUDA(cudaMemcpyAsync(base, leaves, n_leaves * 32, cudaMemcpyHostToDevice, s));
+        d_leaves = base;
+        d_nodes = base + n_leaves * 8;
+    }
+    // every level reads the previous one and writes its own slice of `nodes`, all in `repr`
+    const uint32_t* src = d_leaves;
+    uint32_t* dst = d_nodes;
+    for (size_t pairs = n_leaves / 2; pairs >= 1; pairs /= 2) {
+        SpongeArgs a = base_args(ctx, pairs);
+        a.in = src;
+        a.n_absorb = 2;
+        a.in_layout = kLayoutAos;
+        a.in_repr = repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = 1;
+        a.out = dst;
+        a.out_layout = kLayoutAos;
+        a.out_repr = repr;
+        st = launch(ctx, a, s);
+        if (st != PSD_OK) return st;
+        src = dst;
+        dst += pairs * 8;
+        if (pairs == 1) break;
+    }
+    if (mem == PSD_MEM_DEVICE) return PSD_OK;   // asynchronous on the caller's stream
+    PSD_CUDA(cudaMemcpyAsync(nodes, d_nodes, (n_leaves - 1) * 32, cudaMemcpyDeviceToHost, s));
+    PSD_CUDA(cudaStreamSynchronize(s));
+    return check_err_flag(ctx, s);
+}
+
+extern "C" psd_status psd_merkle_path(const uint64_t* leaves, const uint64_t* nodes, size_t n_leaves, size_t index,
+                                      uint64_t* path) {
+    if (!leaves || !nodes || !path) return fail(PSD_ERR_ARG, "null argument");
+    if (n_leaves < 2 || (n_leaves & (n_leaves - 1)) || index >= n_leaves) return fail(PSD_ERR_ARG, "bad n_leaves/index");
+    const uint64_t* level = leaves;   // current level, `width` elements
+    size_t width = n_leaves, pos = index, next_off = 0;
+    while (width > 1) {
+        memcpy(path, level + (pos ^ 1) * 4, 32);
+        path += 4;
+        level = nodes + next_off * 4;
+        next_off += width / 2;
+        width /= 2;
+        pos /= 2;
+    }
+    return PSD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Merkle root without any allocation (see include/poseidon_b200.h).  The level buffers live in a
 // fixed array inside the library image instead of a cudaMalloc'd block: hosts that give all device
 // memory to their own arena at start-up cannot tolerate a cudaMalloc on the request path.

@@ -240,6 +240,22 @@ class PoseidonContext:
         check(lib.psd_merkle_root(self.handle, _ptr(leaves), leaves.size // 4, _ptr(root), repr, L.MEM_HOST, None))
         return root
 
+    def merkle_tree(self, leaves: np.ndarray, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
+        """All internal nodes, bottom-up (parents of the leaves first, root last): (n_leaves-1, 4)."""
+        assert leaves.dtype == np.uint64 and leaves.flags.c_contiguous and leaves.size % 4 == 0
+        n = leaves.size // 4
+        nodes = np.zeros((n - 1, 4), dtype=np.uint64)
+        check(lib.psd_merkle_tree(self.handle, _ptr(leaves), n, _ptr(nodes), repr, L.MEM_HOST, None))
+        return nodes
+
+    @staticmethod
+    def merkle_path(leaves: np.ndarray, nodes: np.ndarray, index: int) -> np.ndarray:
+        """Authentication path of leaf `index`: the sibling at every level, leaf level first."""
+        n = leaves.size // 4
+        path = np.zeros((max(n.bit_length() - 1, 1), 4), dtype=np.uint64)
+        check(lib.psd_merkle_path(_ptr(leaves), _ptr(nodes), n, index, _ptr(path)))
+        return path[: n.bit_length() - 1]
+
     def to_montgomery(self, elems: np.ndarray) -> np.ndarray:
         check(lib.psd_to_montgomery(self.handle, _ptr(elems), elems.size // 4, L.MEM_HOST, None))
         return elems

@@ -172,6 +172,37 @@ def test_merkle_golden(S, pairs):
     assert r1024 == int(g["bn254_t3_merkle_leaves_1_1024"], 16)
 
 
+@pytest.mark.parametrize("repr_name", ["mont", "canon"])
+def test_merkle_tree_and_paths(S, pairs, repr_name):
+    """psd_merkle_tree returns every internal node; each level equals the oracle's, the last node is
+    psd_merkle_root's root, and an authentication path recomputes the root through compress_pairs."""
+    pr = pairs("bn254_t3")
+    n = 1 << 10
+    leaves_m = pr.orc.synth(n, seed=0xD7)
+    canon = repr_name == "canon"
+    leaves = pr.orc.from_mont(leaves_m.copy()) if canon else leaves_m
+    rep = S.REPR_CANONICAL if canon else S.REPR_MONTGOMERY
+    nodes = pr.ctx.merkle_tree(leaves, repr=rep)
+    assert nodes.shape == (n - 1, 4)
+    level, off = leaves_m, 0
+    while level.shape[0] > 1:
+        nxt = pr.orc.absorb_squeeze_batch(np.ascontiguousarray(level), level.shape[0] // 2, 2, 1).reshape(-1, 4)
+        want = pr.orc.from_mont(nxt.copy()) if canon else nxt
+        assert np.array_equal(nodes[off:off + nxt.shape[0]], want)
+        off += nxt.shape[0]
+        level = nxt
+    assert np.array_equal(nodes[-1], pr.ctx.merkle_root(leaves, repr=rep))
+    for idx in (0, 1, 517, n - 1):
+        path = pr.ctx.merkle_path(leaves, nodes, idx)
+        assert path.shape == (10, 4)
+        cur, pos = leaves[idx], idx
+        for sib in path:
+            pair = np.stack([cur, sib]) if pos % 2 == 0 else np.stack([sib, cur])
+            cur = pr.ctx.compress_pairs(np.ascontiguousarray(pair), repr=rep)[0]
+            pos //= 2
+        assert np.array_equal(cur, nodes[-1])
+
+
 def test_compress_pairs(S, pairs):
     pr = pairs("bn254_t3")
     x = pr.orc.synth(2 * 999, seed=0xD1)
