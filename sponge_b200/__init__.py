@@ -8,4 +8,6 @@ from .poseidon import (DuplexSpongeMode, FieldElementSize, PoseidonConfig, Posei
                        find_poseidon_ark_and_mds, get_default_poseidon_parameters, ints_to_limbs,
                        kernel_launch_count, limbs_to_ints, MODULUS, MODULUS_BIT_SIZE)
 
+from . import absorb  # noqa: F401,E402
+
 __version__ = "0.1.0"

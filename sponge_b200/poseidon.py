@@ -401,7 +401,13 @@ class PoseidonSponge:
             buf = (C.c_uint8 * len(input)).from_buffer_copy(bytes(input)) if len(input) else None
             check(lib.psd_sponge_absorb_bytes(self._h, buf, len(input)))
             return
-        elems = [input] if isinstance(input, int) else list(input)
+        if isinstance(input, int) and not isinstance(input, bool):
+            elems = [input]
+        elif isinstance(input, (list, tuple)) and all(isinstance(e, int) and not isinstance(e, bool) for e in input):
+            elems = list(input)
+        else:   # typed stand-ins for other Rust values (sponge_b200.absorb): u8/ints/bool/Option/lists
+            from .absorb import to_sponge_field_elements
+            elems = to_sponge_field_elements(input, self.parameters.field)
         if not elems:
             return   # mod.rs:234-236
         p = self.parameters.modulus

@@ -237,3 +237,21 @@ def test_cpp_wrapper_reference_kat(S):
     kat = load_golden("reference_kats.json")["sponge_consistency"]["squeeze_native"]
     r = subprocess.run([exe] + ["%064x" % int(v) for v in kat], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_typed_absorb_and_macros(S, ref, fixture_pair):
+    """tests.rs:87-102 (absorb! == sequential absorb) and typed inputs through sponge.absorb:
+    ints, signed ints, byte slices, Option -- against the oracle fed with the same field elements."""
+    from sponge_b200 import absorb as A
+    ocfg, cfg = fixture_pair
+    s1, s2 = S.PoseidonSponge(cfg), S.PoseidonSponge(cfg)
+    v = [A.I32(x) for x in (1, 2, 3, 4, 5, 6)]
+    s1.absorb(v)
+    s1.absorb(114514)
+    A.absorb_all(s2, v, A.Fe(114514))
+    assert s1.squeeze_native_field_elements(3) == s2.squeeze_native_field_elements(3)
+    s3, o = S.PoseidonSponge(cfg), ref.PoseidonSponge(ocfg)
+    for item in ([A.I16(-7), A.U64(9)], bytes(range(40)), A.Some(A.U8(3)), A.NONE, True):
+        s3.absorb(item)
+        o.absorb(A.to_sponge_field_elements(item, "bls12_381"))
+    assert s3.squeeze_native_field_elements(2) == o.squeeze_native_field_elements(2)
