@@ -76,6 +76,15 @@ def oracle_cfg(ref, name, fixture=None):
         elif name == "bn254_odd_rf":    # odd full_rounds: extra full round at the end (mod.rs:96)
             ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 7, 5, 0)
             c = ref.PoseidonConfig(7, 5, 3, mds, ark, 2, 1, ref.BN254_FR)
+        elif name == "bn254_full_only":  # no partial rounds at all
+            ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 6, 0, 0)
+            c = ref.PoseidonConfig(6, 0, 5, mds, ark, 2, 1, ref.BN254_FR)
+        elif name == "bn254_rf1":        # full_rounds / 2 == 0: the optimised form does not apply
+            ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 1, 4, 0)
+            c = ref.PoseidonConfig(1, 4, 5, mds, ark, 2, 1, ref.BN254_FR)
+        elif name == "bls_t3_alpha5":    # BLS12-381 with alpha = 5 (default table, rate 3 has alpha 5 but t = 4)
+            ark, mds = ref.find_poseidon_ark_and_mds(ref.BLS12_381_FR, 255, 2, 8, 56, 0)
+            c = ref.PoseidonConfig(8, 56, 5, mds, ark, 2, 1, ref.BLS12_381_FR)
         else:
             raise KeyError(name)
         _CFG_CACHE[name] = c

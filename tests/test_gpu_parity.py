@@ -9,7 +9,8 @@ from conftest import field_id, field_name, oracle_cfg, to_ints, to_limbs, load_g
 pytestmark = pytest.mark.gpu
 
 CFG_NAMES = ["bn254_t3", "bn254_t5", "bls_default_r2", "bls_fixture", "bls_default_r3", "bls_default_r2_w",
-             "bn254_t2", "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r5", "bls_default_r8"]
+             "bn254_t2", "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r5", "bls_default_r8",
+             "bn254_full_only", "bn254_rf1", "bls_t3_alpha5"]
 
 
 @pytest.fixture(scope="module")

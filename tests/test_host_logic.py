@@ -162,7 +162,8 @@ def test_device_arithmetic_host_model(emu, ref, field):
 
 
 @pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bls_default_r2", "bls_fixture", "bn254_t2",
-                                  "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r2_w"])
+                                  "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r2_w", "bn254_full_only",
+                                  "bn254_rf1", "bls_t3_alpha5"])
 def test_permutation_variants_host_model(emu, ref, name):
     """The device permutation code (poseidon_core.cuh: dense, optimised sparse/lazy form, rolled form)
     compiled for the host with the product's own constant derivation (opt_constants.cpp), against the
@@ -183,13 +184,16 @@ def test_permutation_variants_host_model(emu, ref, name):
     variants = [0, 1, 2, 3]          # dense, optimised, rolled, compact optimised
     if t <= 3:
         variants.append(4)           # compact optimised with digit-table constant products
-    if cfg.partial_rounds and cfg.full_rounds >= 2:
+    if cfg.partial_rounds and cfg.full_rounds >= 2 and t <= 5:
         variants.append(5)           # ... with tables for the lane updates only (the t = 5 mode)
     for variant in variants:
         s = st.copy().view(np.uint32)
         rc = emu.emu_permute(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
                              C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), variant,
                              C.c_void_p(s.ctypes.data), C.c_size_t(n))
+        if rc == 1:      # the requested optimised form does not exist for this parameter set (e.g. full_rounds < 2)
+            assert cfg.full_rounds < 2
+            continue
         assert rc == 0, (variant, rc)
         assert np.array_equal(s.view(np.uint64), exp), f"variant {variant} differs from the oracle"
 
