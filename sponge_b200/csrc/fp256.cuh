@@ -482,7 +482,10 @@ PSD_DEV void mont_row(uint32_t* x, uint32_t* y, const uint32_t* a, uint32_t bi) 
 // V_i <= V_{i-1}/2^32 + (2^32-1)(a+p) < 2^288, so the hi-aligned accumulator (columns 1..8) never
 // carries out, and the result is < a + p <= 2p: one conditional subtraction.
 // 128 IMAD.WIDE.U32 + 8 IMAD = 136 integer multiplies (SURVEY.md 8(d) unit of work).
-template <class F>
+//
+// REDUCE = false leaves the result in [0, a*b/2^256 + p) without the conditional subtraction (BN254
+// only; see sbox_compact's LAZY mode for the bounds that make this safe).
+template <class F, bool REDUCE = true>
 PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     uint32_t e[8], o[8];
     mul4(e, a[0], a[2], a[4], a[6], b[0]);
@@ -495,9 +498,13 @@ PSD_DEV void mont_mul(uint32_t* r, const uint32_t* a, const uint32_t* b) {
     mont_row<F>(e, o, a, b[5]);
     mont_row<F>(o, e, a, b[6]);
     mont_row<F>(e, o, a, b[7]);
-    uint32_t s[8];
-    merge8(s, e, o);        // o[0] == 0 here
-    cond_sub_p<F>(r, s);
+    if (REDUCE) {
+        uint32_t s[8];
+        merge8(s, e, o);        // o[0] == 0 here
+        cond_sub_p<F>(r, s);
+    } else {
+        merge8(r, e, o);
+    }
 }
 
 // r = (sum_{j<N} a[j] * b[j]) * 2^-256 mod p with ONE interleaved Montgomery reduction ("lazy"
@@ -561,7 +568,9 @@ PSD_DEV void sqr_row(uint32_t* x, uint32_t* y, const uint32_t* v, uint32_t ai) {
 // bit of a_{j-1}; for row i that bit is masked off limb i+1, so the row adds
 // a_i * (a_i*2^(32i) + 2*(a >> 32(i+1)) << 32(i+1))).  Needs 3p < 2^256 for the 9-limb window
 // (row multiplicand < 2a < 2p, plus m*p), i.e. BN254 Fr; F::kSqrNineLimb says so.
-template <class F>
+// Accepts any a with 2a + p < 2^256 (BN254: a < 2.14 p), so an unreduced result of a previous
+// REDUCE = false squaring can be squared again; REDUCE = false returns a value < a^2/2^256 + p.
+template <class F, bool REDUCE = true>
 PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
     uint32_t d[8];
 #if !defined(PSD_HOST_EMU)
@@ -594,9 +603,13 @@ PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
     PSD_SQR_ROW(6, o, e)
     PSD_SQR_ROW(7, e, o)
 #undef PSD_SQR_ROW
-    uint32_t s[8];
-    merge8(s, e, o);
-    cond_sub_p<F>(r, s);
+    if (REDUCE) {
+        uint32_t s[8];
+        merge8(s, e, o);
+        cond_sub_p<F>(r, s);
+    } else {
+        merge8(r, e, o);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1025,10 +1038,10 @@ PSD_DEV void neg_if_larger_half(uint32_t* b, const uint32_t* a) {
 }
 
 // Squaring entry point used by the S-box: dedicated squaring where its bound holds.
-template <class F>
+template <class F, bool REDUCE = true>
 PSD_DEV void fp_sqr(uint32_t* r, const uint32_t* a) {
     if (F::kBits == 254) {
-        mont_sqr<F>(r, a);
+        mont_sqr<F, REDUCE>(r, a);
     } else {
         // BLS12-381: 3p > 2^256, so mont_sqr's 9-limb window could overflow for a close to p; the wide
         // variant (mont_sqr_w) works but its carry handling makes it slower than a plain product on

@@ -266,8 +266,15 @@ PSD_DEV void permute_opt(uint32_t (&st)[T][8], const PermDesc& d) {
 //   phase B: nB x { t = <coeff row i, s>; shift t into n }             nB = T (full) | 1 (partial)
 //   phase C: partial only, (T-1) x { s1 += v_j * s0; rotate lanes 1..T-1 }
 // ------------------------------------------------------------------------------------------------
-template <class F, int ALPHA>
+// LAZY (BN254 Fr only, p = 0.189 * 2^256): the three conditional subtractions inside x^alpha are
+// dropped and the result is left in [0, 1.25 p).  With x < p on entry: x^2 < (1 + 0.189) p, and a
+// squaring of a < 1.33 p stays below (1 + 1.33^2 * 0.189) p < 1.34 p, inside mont_sqr's operand bound
+// 2a + p < 2^256; the closing product has a = y < 1.34 p (a + p < 2^256) and b = x < p, giving
+// < (1 + 1.34 * 0.189) p < 1.26 p.  Only callers whose consumers take any 256-bit value may ask for
+// it: const_dot reads the value digit by digit and its bounds do not depend on the operand.
+template <class F, int ALPHA, bool LAZY = false>
 PSD_DEV void sbox_compact(uint32_t* x, const PermDesc& d) {
+    static_assert(!LAZY || (F::kBits == 254 && (ALPHA == 5 || ALPHA == 17)), "lazy S-box: BN254, alpha 5/17 only");
     if (ALPHA == 5 || ALPHA == 17) {
         uint32_t y[8];
 #pragma unroll
@@ -275,8 +282,8 @@ PSD_DEV void sbox_compact(uint32_t* x, const PermDesc& d) {
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-        for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F>(y, y);
-        mont_mul<F>(x, y, x);
+        for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, !LAZY>(y, y);
+        mont_mul<F, !LAZY>(x, y, x);
     } else {
         sbox<F, ALPHA>(x, d);
     }
@@ -379,6 +386,7 @@ PSD_DEV void row_cdot(uint32_t* out, const uint32_t (*st)[8], uint32_t off_first
 // fit the constant pool, e.g. t = 5); rows stay lazily reduced Montgomery dot products as in variant 2.
 template <class F, int T, int ALPHA, bool LANES_ONLY = false>
 PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
+    constexpr bool kLazySbox = !LANES_ONLY && F::kBits == 254 && (ALPHA == 5 || ALPHA == 17);
     const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
 #if defined(__CUDACC__)
 #pragma unroll 1
@@ -400,7 +408,8 @@ PSD_DEV void permute_opt_ctab(uint32_t (&st)[T][8], const PermDesc& d) {
             uint32_t c[8];
             cload8(c, ark + i * 8);
             fp_add<F>(st[0], st[0], c);
-            sbox_compact<F, ALPHA>(st[0], d);
+            // every consumer of an S-box output below is a const_dot unless LANES_ONLY
+            sbox_compact<F, ALPHA, kLazySbox>(st[0], d);
             if (full) {
 #pragma unroll
                 for (int k = 0; k < 8; k++) {

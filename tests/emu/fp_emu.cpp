@@ -118,6 +118,18 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }
 
+// BN254 S-box without its inner conditional subtractions (sbox_compact's LAZY mode): raw 256-bit result
+extern "C" void emu_sbox_lazy_bn254(uint64_t alpha, uint32_t* r, const uint32_t* a, size_t n) {
+    PermDesc d{};
+    for (size_t i = 0; i < n; i++) {
+        uint32_t x[8];
+        memcpy(x, a + 8 * i, 32);
+        if (alpha == 5) sbox_compact<Bn254Fr, 5, true>(x, d);
+        else sbox_compact<Bn254Fr, 17, true>(x, d);
+        memcpy(r + 8 * i, x, 32);
+    }
+}
+
 extern "C" void emu_mont_sqr(int field, uint32_t* r, const uint32_t* a, size_t n) {
     for (size_t i = 0; i < n; i++) {
         if (field == 0) mont_sqr<Bn254Fr>(r + 8 * i, a + 8 * i);

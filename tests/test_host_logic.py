@@ -198,6 +198,25 @@ def test_permutation_variants_host_model(emu, ref, name):
         assert np.array_equal(s.view(np.uint64), exp), f"variant {variant} differs from the oracle"
 
 
+def test_lazy_sbox_host_model(emu, ref):
+    """BN254 S-box with the inner conditional subtractions dropped (digit-table variant): the raw result is
+    congruent to x^alpha, stays below the 1.26 p bound stated in poseidon_core.cuh, also for x = p - 1."""
+    p = ref.BN254_FR
+    rng = random.Random(77)
+    rinv = pow(1 << 256, -1, p)
+    n = 3000
+    A = [rng.randrange(p) for _ in range(n)]
+    A[:8] = [0, 1, p - 1, p - 2, (1 << 253) - 1, 1 << 253, 0xffffffff, p // 2]
+    a = to_limbs(A).view(np.uint32)
+    for alpha in (5, 17):
+        r = np.zeros_like(a)
+        emu.emu_sbox_lazy_bn254(C.c_uint64(alpha), C.c_void_p(r.ctypes.data), C.c_void_p(a.ctypes.data), C.c_size_t(n))
+        got = to_ints(r.view(np.uint64))
+        for x, g in zip(A, got):
+            assert g % p == pow(x, alpha, p) * pow(rinv, alpha - 1, p) % p
+            assert g * 100 < 126 * p
+
+
 def test_mont_dot_host_model(emu, ref):
     """Lazily reduced dot product (one Montgomery reduction for N products), BN254, worst-case operands."""
     p = ref.BN254_FR
