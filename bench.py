@@ -469,7 +469,7 @@ def main():
                 warmup=max(args.warmup, 3), ms_per_step=ms_per_step, higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="u32x8 (256-bit Montgomery residues, 8x32-bit limbs)", data="synthetic",
                 config=dict(workload=f"{name}: {w['desc']}", units_per_gpu_per_step=units,
-                            permutations_per_unit=perms_per_unit, kernel_variant=args.variant,
+                            permutations_per_unit=perms_per_unit, kernel_variant=ctx.active_variant(), kernel_variant_requested=args.variant,
                             layout="AoS Montgomery, device-resident, in place",
                             l2="inputs larger than L2 (no flush needed)" if alg_bytes > (252 << 20) else "inputs fit L2",
                             per_step_ms=[round(x, 4) for x in per_step_ms]),

@@ -29,18 +29,18 @@ for f in 0 1; do
     fi
   done
 done
-for u in misc_kernels api; do
+for u in misc_kernels api tu_fp52; do
   o=$OBJ/$u.o
   if newer $o $SRC/$u.cu $HDRS; then run $NVCC $NVFLAGS -c -o $o $SRC/$u.cu; fi
 done
-for u in params opt_constants; do
+for u in params opt_constants fp52_tables; do
   o=$OBJ/$u.o
   if newer $o $SRC/$u.cpp $HDRS; then run g++ -O2 -std=c++17 -fPIC -c -o $o $SRC/$u.cpp; fi
 done
 fail=0
 for p in "${pids[@]:-}"; do [[ -n "$p" ]] && { wait "$p" || fail=1; }; done
 [[ $fail -eq 0 ]] || { echo "build failed" >&2; exit 1; }
-OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/params.o $OBJ/opt_constants.o"
+OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o"
 for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o"; done; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $LIB/libposeidon_b200.so $OBJS -Xcompiler -fPIC
 # CPU oracle (test infrastructure)
@@ -48,7 +48,8 @@ if newer oracle/liboracle.so oracle/poseidon_oracle.c; then
   gcc -O3 -fopenmp -shared -fPIC -o oracle/liboracle.so oracle/poseidon_oracle.c
 fi
 # host emulation of the device arithmetic (test infrastructure)
-if newer tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $SRC/opt_constants.cpp $SRC/params.cpp $HDRS; then
-  g++ -O2 -std=c++17 -shared -fPIC -o tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $SRC/opt_constants.cpp $SRC/params.cpp
+if newer tests/emu/libfp_emu.so tests/emu/fp_emu.cpp $SRC/opt_constants.cpp $SRC/fp52_tables.cpp $SRC/params.cpp $HDRS; then
+  g++ -O2 -std=c++17 -frounding-math -ffp-contract=off -shared -fPIC -o tests/emu/libfp_emu.so tests/emu/fp_emu.cpp \
+    $SRC/opt_constants.cpp $SRC/fp52_tables.cpp $SRC/params.cpp
 fi
 echo "built $LIB/libposeidon_b200.so"

@@ -254,10 +254,15 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 0 = dense (ark -> S-box -> dense MDS every round, the reference's operation order),
  * 1 = optimised, fully unrolled rounds,
  * 2 = optimised, compact rolled phases,
- * 3 = 2 + products by round constants through digit tables (default).  The tables take about 33 KB
- *     of the 62 KB constant pool that the contexts of one (field, width) share, so only the first
- *     live t=3 context of each field gets them; every other context silently runs variant 2. */
+ * 3 = 2 + products by round constants through digit tables.  The tables take about 33 KB of the
+ *     62 KB constant pool that the contexts of one (field, width) share, so only the first live t=3
+ *     context of each field gets them; every other context silently runs variant 2.  (4 is an alias.)
+ * 5 = integer S-box + the whole linear layer on the FP64 pipe in 52-bit limbs (BN254 Fr, t <= 3,
+ *     alpha 5 or 17).  Its tables (about 54 KB) live in a separate constant pool that one parameter
+ *     set nearly fills: the first live eligible context gets it, every other one runs as variant 3.
+ * psd_ctx_active_variant reports what a launch on this context really runs (0..5; 4 = the t=5 form of 3). */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
+psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant);
 
 #ifdef __cplusplus
 }

@@ -104,6 +104,7 @@ _PROTOS = {
     "psd_kernel_launch_count": (_u64, []),
     "psd_imad_peak": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "psd_ctx_set_variant": (_i, [_vp, _i]),
+    "psd_ctx_active_variant": (_i, [_vp, C.POINTER(C.c_int)]),
 }
 
 for _name, (_res, _args) in _PROTOS.items():

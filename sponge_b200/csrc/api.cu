@@ -17,6 +17,7 @@
 
 #include "../../include/poseidon_b200.h"
 #include "kernels.cuh"
+#include "fp52_tables.hpp"
 #include "opt_constants.hpp"
 #include "params.hpp"
 #include "registry.hpp"
@@ -99,7 +100,7 @@ struct DevicePool {
     std::mutex mu;
     std::vector<PoolSlot> used;   // sorted by off
 };
-static DevicePool g_pools[64][2][10];
+static DevicePool g_pools[64][2][kFp52PoolKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool
 static std::once_flag g_misc_once[64];
 static inline uint32_t misc_one_off(int field) { return (uint32_t)field * 16; }
 static inline uint32_t misc_r2_off(int field) { return (uint32_t)field * 16 + 8; }
@@ -156,6 +157,10 @@ struct psd_ctx {
     PermDesc misc_desc{};  // same parameters with one/r2 offsets of the small-kernel unit's pool
     uint32_t pool_off = 0, pool_len = 0;
     bool pool_held = false;
+    // variant 5 (tu_fp52.cu) has its own pool and descriptor; fdesc.fp_ok == 0 when the context has none
+    PermDesc fdesc{};
+    uint32_t fpool_off = 0, fpool_len = 0;
+    bool fpool_held = false;
     int variant = 3;   // falls back to 2 when the context has no digit tables
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
@@ -258,15 +263,30 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
     return cfg;
 }
 
-psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
+// the kernel variant a launch really uses: the requested one, degraded to what this context has
+// constants for
+int resolve_variant(const psd_ctx* ctx) {
+    if (ctx->variant >= 5 && ctx->fdesc.fp_ok) return 5;
     int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
     if (variant >= 3) variant = ctx->desc.ctab_ok == 1 ? 3 : ctx->desc.ctab_ok == 2 ? 4 : 2;
+    return variant;
+}
+
+psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
+    const int variant = resolve_variant(ctx);
+    const bool fp52 = variant == 5;
     const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
     if (a.n > (uint64_t)0x7fffffff * 128) return fail(PSD_ERR_ARG, "batch too large for one launch (%llu sponges)", (unsigned long long)a.n);
     LaunchCfg cfg = sponge_cfg(ctx, k, a.n);
-    k->fn<<<cfg.grid, cfg.block, 0, stream>>>(a);
+    if (fp52) {
+        SpongeArgs b = a;
+        b.d = ctx->fdesc;   // same parameters, offsets into the variant-5 unit's pool
+        k->fn<<<cfg.grid, cfg.block, 0, stream>>>(b);
+    } else {
+        k->fn<<<cfg.grid, cfg.block, 0, stream>>>(a);
+    }
     g_launches.fetch_add(1, std::memory_order_relaxed);
     PSD_CUDA(cudaGetLastError());
     return PSD_OK;
@@ -582,6 +602,30 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->pool_held = true;
     offset_desc(ctx->desc, ctx->pool_off);
 
+    // Variant 5 (FP64-pipe linear layer): its own image [ark][mds][one][r2][52-bit-limb tables] in the
+    // pool of tu_fp52.cu, for the parameter sets that unit has kernels for, when that pool has room
+    // (one parameter set nearly fills it, so in practice the first live context gets it).
+    std::vector<uint32_t> fimg;
+    {
+        const SpongeKernelEntry* fk = find_kernel(p->field, (int)t, p->alpha, 5);
+        if (fk && fk->variant == 5 && fk->alpha == p->alpha) {
+            PermDesc fd = base_desc;
+            fd.opt_ok = fd.ctab_ok = 0;
+            fd.pre_mds_off = fd.sparse_off = fd.post_ark_off = 0;
+            fimg.assign(img.begin(), img.begin() + base_desc.r2_off + 8);   // [ark][mds][one][r2]
+            append_fp52_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, fd, fimg);
+            if (fd.fp_ok && fimg.size() <= kConstPoolWords &&
+                pool_alloc(device, p->field, kFp52PoolKey, (uint32_t)fimg.size(), &ctx->fpool_off, nullptr)) {
+                ctx->fpool_len = (uint32_t)fimg.size();
+                ctx->fpool_held = true;
+                offset_desc(fd, ctx->fpool_off);
+                ctx->fdesc = fd;
+            } else {
+                fimg.clear();
+            }
+        }
+    }
+
     auto cleanup = [&](psd_status s) {
         psd_ctx_destroy(ctx);
         return s;
@@ -604,6 +648,11 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
         PoolUploadFn up = find_uploader(ctx->field, (int)t);
         if (!up) return cleanup(fail(PSD_ERR_UNSUPPORTED, "no kernels for field %d, t=%u in this build", ctx->field, t));
         CTX_CUDA(up(ctx->pool_off, img.data(), (uint32_t)img.size(), nullptr));
+        if (ctx->fpool_held) {
+            PoolUploadFn fup = find_uploader(ctx->field, kFp52PoolKey);
+            if (!fup) return cleanup(fail(PSD_ERR_UNSUPPORTED, "variant-5 kernels without a pool uploader"));
+            CTX_CUDA(fup(ctx->fpool_off, fimg.data(), (uint32_t)fimg.size(), nullptr));
+        }
         // [R, R^2] of both fields for the small kernels (convert / synth), once per device
         cudaError_t misc_err = cudaSuccess;
         std::call_once(g_misc_once[device], [&] {
@@ -658,6 +707,7 @@ static void ctx_teardown(psd_ctx* ctx) {
         if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
     }
     if (ctx->pool_held) pool_free(ctx->device, ctx->field, (int)ctx->t, ctx->pool_off);
+    if (ctx->fpool_held) pool_free(ctx->device, ctx->field, kFp52PoolKey, ctx->fpool_off);
     delete ctx;
 }
 
@@ -677,8 +727,16 @@ psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
 
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
     if (!ctx) return fail(PSD_ERR_ARG, "null context");
-    if (variant < 0 || variant > 3) return fail(PSD_ERR_ARG, "variant must be 0..3");
+    if (variant < 0 || variant > 5) return fail(PSD_ERR_ARG, "variant must be 0..5");
     ctx->variant = variant;
+    return PSD_OK;
+}
+
+psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant) {
+    if (!ctx || !variant) return fail(PSD_ERR_ARG, "null argument");
+    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, resolve_variant(ctx));
+    if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
+    *variant = k->variant;
     return PSD_OK;
 }
 

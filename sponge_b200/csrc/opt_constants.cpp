@@ -232,6 +232,13 @@ void offset_desc(PermDesc& d, uint32_t pool_off) {
     d.pre_mds_off += pool_off;
     d.sparse_off += pool_off;
     d.post_ark_off += pool_off;
+    // 8-byte units; slots are multiples of 8 words, so pool_off is even
+    d.fp_consts_off += pool_off / 2;
+    d.fp_mat_off += pool_off / 2;
+    d.fp_pre_off += pool_off / 2;
+    d.fp_last_off += pool_off / 2;
+    d.fp_k_off += pool_off / 2;
+    d.fp_part_off += pool_off / 2;
 }
 
 }  // namespace psd

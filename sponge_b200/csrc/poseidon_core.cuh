@@ -18,7 +18,7 @@ constexpr uint32_t kConstPoolWords = 15872;
 #if defined(__CUDACC__)
 __constant__ __align__(16) uint32_t c_pool[kConstPoolWords];
 #else
-static uint32_t c_pool[kConstPoolWords];
+alignas(16) static uint32_t c_pool[kConstPoolWords];
 #endif
 
 // One field element (8 words) from the pool.  Offsets are multiples of 8 words, so this is two
@@ -60,6 +60,15 @@ struct PermDesc {
     uint32_t ct_mds_off;    // [T][T][4][8]          tables of the dense matrix
     uint32_t ct_pre_off;    // [T][T][4][8]          tables of M_pre
     uint32_t ct_sparse_off; // [partial][2(T-1)][4][8]: w_1..w_{T-1}, v_1..v_{T-1} per partial round
+    // FP64-pipe constant products (fp52.cuh / poseidon_fp52.cuh, VARIANT 5); valid when fp_ok != 0.
+    // Offsets in 8-BYTE units into the pool of the unit that holds the variant-5 kernels.
+    uint32_t fp_ok;
+    uint32_t fp_consts_off; // P52[5], NP52, SHIFT, 2^104
+    uint32_t fp_mat_off;    // [T][T][5][5] doubles: tables of the dense matrix (row-major; [0][0] doubles as M00)
+    uint32_t fp_pre_off;    // same shape: M_pre
+    uint32_t fp_last_off;   // same shape: the matrix of the last partial round (sparse row + lane updates + rescale)
+    uint32_t fp_k_off;      // additive constants, 6 int64 per row, in execution order
+    uint32_t fp_part_off;   // [partial-1][2(T-1)][5][5] doubles: w_1.., v_1.. tables per partial round but the last
 };
 
 template <class F, int ALPHA>

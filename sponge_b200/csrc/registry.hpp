@@ -16,10 +16,13 @@ typedef void (*SpongeKernelFn)(const SpongeArgs);
 struct SpongeKernelEntry {
     int field, t;
     uint64_t alpha;     // 0 = any alpha (runtime ladder)
-    int variant;        // 0 = dense, 1 = optimised
+    int variant;        // 0 = dense ... 5 = FP64-pipe linear layer (see psd_ctx_set_variant)
     SpongeKernelFn fn;
     const char* name;
 };
+
+// Pool key of the FP64-pipe unit (tu_fp52.cu), used in place of t for its pool and uploader.
+constexpr int kFp52PoolKey = 10;
 
 // field/t identify the translation unit's kernels; the small-kernel unit registers as (-1, 0)
 void register_pool_uploader(int field, int t, PoolUploadFn fn);

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include "kernels.cuh"
+#include "poseidon_fp52.cuh"
 
 namespace psd {
 
@@ -48,7 +49,9 @@ __device__ __forceinline__ void store_elem(const uint32_t* x, uint32_t* base, in
 // ------------------------------------------------------------------------------------------------
 template <class F, int T, int ALPHA, int VARIANT>
 __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d) {
-    if constexpr (T > 5) {
+    if constexpr (VARIANT == 5) {
+        permute_fp52<F, T, ALPHA>(st, d);       // the host only selects this kernel when d.fp_ok
+    } else if constexpr (T > 5) {
         permute_rolled<F, T, ALPHA>(st, d);
     } else if constexpr (VARIANT == 4) {
         permute_opt_ctab<F, T, ALPHA, true>(st, d);    // lane-update tables only (d.ctab_ok == 2)
@@ -71,9 +74,15 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #ifndef PSD_MIN_BLOCKS
 #define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 7 : (T) == 5 ? 5 : 0)   /* 0 = no hint; t=5: 83.8 M vs 83.0 M hash/s */
 #endif
+// Variant 5 keeps the state in 52-bit limb pairs next to the integer S-box temporaries and needs more
+// registers than the integer kernels.
+#ifndef PSD_MIN_BLOCKS_FP52
+#define PSD_MIN_BLOCKS_FP52 5
+#endif
+#define PSD_KERNEL_MIN_BLOCKS(T, VARIANT) ((VARIANT) == 5 ? PSD_MIN_BLOCKS_FP52 : PSD_MIN_BLOCKS(T))
 
 template <class F, int T, int ALPHA, int VARIANT>
-__global__ void __launch_bounds__(128, PSD_MIN_BLOCKS(T)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+__global__ void __launch_bounds__(128, PSD_KERNEL_MIN_BLOCKS(T, VARIANT)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
     const PermDesc& d = a.d;
     const uint32_t rate = d.rate, cap = d.capacity;
     bool bad = false;

@@ -202,6 +202,12 @@ class PoseidonContext:
     def set_variant(self, variant: int) -> None:
         check(lib.psd_ctx_set_variant(self.handle, variant))
 
+    def active_variant(self) -> int:
+        """The kernel variant a launch on this context really runs (requested variant after fallbacks)."""
+        v = C.c_int(0)
+        check(lib.psd_ctx_active_variant(self.handle, C.byref(v)))
+        return v.value
+
     # -- host-array batch calls ---------------------------------------------------------------
     def permute_batch(self, states: np.ndarray, layout: int = L.LAYOUT_AOS, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
         """n independent `permute`s (mod.rs:95-118), in place on a uint64 array holding n*t elements."""

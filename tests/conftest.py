@@ -82,6 +82,12 @@ def oracle_cfg(ref, name, fixture=None):
         elif name == "bn254_rf1":        # full_rounds / 2 == 0: the optimised form does not apply
             ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 1, 4, 0)
             c = ref.PoseidonConfig(1, 4, 5, mds, ark, 2, 1, ref.BN254_FR)
+        elif name == "bn254_rp1":        # one partial round: it is also the last one (variant 5 runs it as T rows)
+            ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 4, 1, 0)
+            c = ref.PoseidonConfig(4, 1, 5, mds, ark, 2, 1, ref.BN254_FR)
+        elif name == "bn254_rp2_alpha17":  # two partial rounds, alpha = 17 on BN254
+            ark, mds = ref.find_poseidon_ark_and_mds(ref.BN254_FR, 254, 2, 6, 2, 0)
+            c = ref.PoseidonConfig(6, 2, 17, mds, ark, 2, 1, ref.BN254_FR)
         elif name == "bls_t3_alpha5":    # BLS12-381 with alpha = 5 (default table, rate 3 has alpha 5 but t = 4)
             ark, mds = ref.find_poseidon_ark_and_mds(ref.BLS12_381_FR, 255, 2, 8, 56, 0)
             c = ref.PoseidonConfig(8, 56, 5, mds, ark, 2, 1, ref.BLS12_381_FR)

@@ -47,8 +47,23 @@ extern "C" void emu_mont_dot(int n_terms, uint32_t* r, const uint32_t* a, const 
 // host code (params.cpp / opt_constants.cpp) ------------------------------------------------------
 #include <vector>
 
+#include <fenv.h>
+
+#include "../../sponge_b200/csrc/fp52_tables.hpp"
 #include "../../sponge_b200/csrc/opt_constants.hpp"
 #include "../../sponge_b200/csrc/poseidon_core.cuh"
+#include "../../sponge_b200/csrc/poseidon_fp52.cuh"
+
+// the FP64-pipe variant exists for BN254 Fr with alpha 5 / 17 only
+template <class F, int T, int ALPHA>
+static bool emu_perm_fp52(uint32_t (&s)[T][8], const PermDesc& d) {
+    if constexpr (F::kBits == 254 && (ALPHA == 5 || ALPHA == 17) && T <= 5) {
+        permute_fp52<F, T, ALPHA>(s, d);
+        return true;
+    } else {
+        return false;
+    }
+}
 
 template <class F, int T, int ALPHA>
 static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
@@ -60,6 +75,7 @@ static void emu_perm_t(const PermDesc& d, int variant, uint32_t* st, size_t n) {
         else if (variant == 3 && d.opt_ok) permute_opt_compact<F, T, ALPHA>(s, d);
         else if (variant == 4 && d.ctab_ok == 1) permute_opt_ctab<F, T, ALPHA>(s, d);
         else if (variant == 5 && d.ctab_ok == 2) permute_opt_ctab<F, T, ALPHA, true>(s, d);
+        else if (variant == 6 && d.fp_ok && emu_perm_fp52<F, T, ALPHA>(s, d)) {}
         else permute_dense<F, T, ALPHA>(s, d);
         memcpy(st + i * T * 8, s, sizeof s);
     }
@@ -106,14 +122,20 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     Fe r2; memcpy(r2.v, hf->r2, 32); push(r2);
     d.half_full = rf / 2; d.partial = rp; d.total = rounds; d.rate = rate; d.capacity = capacity;
     d.alpha_lo = (uint32_t)alpha; d.alpha_hi = (uint32_t)(alpha >> 32);
-    append_optimised_constants(*hf, t, rf, rp, ark, mds, d, img);
+    if (variant != 6) append_optimised_constants(*hf, t, rf, rp, ark, mds, d, img);
     if (variant == 4) append_digit_tables(*hf, t, rf, rp, mds, d, img);
     if (variant == 5) append_digit_tables(*hf, t, rf, rp, mds, d, img, true);
-    if (img.size() > kConstPoolWords) return -2;
+    if (variant == 6) append_fp52_tables(*hf, t, rf, rp, ark, mds, d, img);
+    if (img.size() > kConstPoolWords) return variant == 6 ? 1 : -2;   // variant 6: tables of wide states exceed the bank
     memcpy(c_pool, img.data(), img.size() * 4);
+    // fp52.cuh's host model is fma() under round-toward-zero (the device uses fma.rz.f64)
+    const int old_round = fegetround();
+    fesetround(FE_TOWARDZERO);
     int rc = field == 0 ? emu_perm_f<Bn254Fr>(d, t, alpha, variant, states, n)
                         : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
+    fesetround(old_round);
     if (rc) return rc;
+    if (variant == 6 && !(d.fp_ok && field == 0 && (alpha == 5 || alpha == 17) && t <= 5)) return 1;
     if ((variant == 4 && d.ctab_ok != 1) || (variant == 5 && d.ctab_ok != 2)) return 1;
     return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }

@@ -128,11 +128,15 @@ def emu():
     so = os.path.join(ROOT, "tests", "emu", "libfp_emu.so")
     csrc = os.path.join(ROOT, "sponge_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "emu", "fp_emu.cpp"), os.path.join(csrc, "opt_constants.cpp"),
+            os.path.join(csrc, "fp52_tables.cpp"),
             os.path.join(csrc, "params.cpp")]
     deps = srcs + [os.path.join(csrc, h) for h in ("fp256.cuh", "poseidon_core.cuh", "opt_constants.hpp",
-                                                   "host_field.hpp", "params.hpp")]
+                                                   "host_field.hpp", "params.hpp", "fp52.cuh", "poseidon_fp52.cuh",
+                                                   "fp52_tables.hpp")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", so] + srcs)
+        # -frounding-math: fp52.cuh's host model runs fma() under FE_TOWARDZERO
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-frounding-math", "-ffp-contract=off", "-shared", "-fPIC",
+                               "-o", so] + srcs)
     return C.CDLL(so)
 
 
@@ -163,7 +167,7 @@ def test_device_arithmetic_host_model(emu, ref, field):
 
 @pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bls_default_r2", "bls_fixture", "bn254_t2",
                                   "bn254_t4_cap2", "bn254_odd_rf", "bls_default_r2_w", "bn254_full_only",
-                                  "bn254_rf1", "bls_t3_alpha5"])
+                                  "bn254_rf1", "bls_t3_alpha5", "bn254_rp1", "bn254_rp2_alpha17"])
 def test_permutation_variants_host_model(emu, ref, name):
     """The device permutation code (poseidon_core.cuh: dense, optimised sparse/lazy form, rolled form)
     compiled for the host with the product's own constant derivation (opt_constants.cpp), against the
@@ -186,6 +190,8 @@ def test_permutation_variants_host_model(emu, ref, name):
         variants.append(4)           # compact optimised with digit-table constant products
     if cfg.partial_rounds and cfg.full_rounds >= 2 and t <= 5:
         variants.append(5)           # ... with tables for the lane updates only (the t = 5 mode)
+    if fid == 0 and cfg.alpha in (5, 17) and t <= 3 and cfg.full_rounds >= 2:   # wider states: tables exceed the bank
+        variants.append(6)           # linear layer in 52-bit limbs on the FP64 pipe (fma under round-toward-zero)
     for variant in variants:
         s = st.copy().view(np.uint32)
         rc = emu.emu_permute(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
