@@ -63,9 +63,10 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--log-n", type=int, default=None, help="override log2(units per GPU)")
-    ap.add_argument("--variant", type=int, default=3,
+    ap.add_argument("--variant", type=int, default=5,
                     help="0 = dense kernel, 1 = optimised unrolled, 2 = optimised compact, "
-                         "3 = compact + digit-table constant products (library default)")
+                         "3 = compact + digit-table constant products, 5 = integer S-box + FP64-pipe linear "
+                         "layer (library default; BN254 t<=3, otherwise runs as 3)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target duration of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")

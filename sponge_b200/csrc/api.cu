@@ -161,7 +161,7 @@ struct psd_ctx {
     PermDesc fdesc{};
     uint32_t fpool_off = 0, fpool_len = 0;
     bool fpool_held = false;
-    int variant = 3;   // falls back to 2 when the context has no digit tables
+    int variant = 5;   // degrades to 3 / 2 / 0 by what the context has constants for (resolve_variant)
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;

@@ -161,9 +161,10 @@ void append_fp52_tables(const HostField& f, uint32_t t, uint32_t full_rounds, ui
             push_k(img, f, pow2, k_lane0[r - half + 1], t);
         }
     }
-    // partial rounds but the last: w tables (row, two Montgomery rows) and v tables (lane update)
+    // every partial round: w tables (row 0, two Montgomery rows) and v tables (lane update; the last
+    // round's are never read -- its lanes go through the `last` matrix -- but keep the stride)
     d.fp_part_off = here();
-    for (uint32_t i = 0; i + 1 < rp; i++) {
+    for (uint32_t i = 0; i < rp; i++) {
         for (uint32_t j = 0; j < n; j++) push_table(img, f, pow2, w[i][j], 104 + 52L * i);
         for (uint32_t j = 0; j < n; j++) push_table(img, f, pow2, v[i][j], -52L * i);
     }

@@ -68,7 +68,7 @@ struct PermDesc {
     uint32_t fp_pre_off;    // same shape: M_pre
     uint32_t fp_last_off;   // same shape: the matrix of the last partial round (sparse row + lane updates + rescale)
     uint32_t fp_k_off;      // additive constants, 6 int64 per row, in execution order
-    uint32_t fp_part_off;   // [partial-1][2(T-1)][5][5] doubles: w_1.., v_1.. tables per partial round but the last
+    uint32_t fp_part_off;   // [partial][2(T-1)][5][5] doubles: w_1.., v_1.. tables per partial round
 };
 
 template <class F, int ALPHA>

@@ -65,6 +65,85 @@ PSD_DEV void f52_lane_update(uint64_t* lane, const double* y, uint32_t tab_off, 
     for (int k = 0; k < 5; k++) lane[k] = c[k] | kMagicLo;
 }
 
+// c = K + sum over lanes j >= 1 of lane_j * TW_j: the part of a partial round's row that does not
+// depend on the S-box output of that round.
+template <int T>
+PSD_DEV void f52_row_lanes(uint64_t* c, const uint64_t (*S)[5], uint32_t tw_off, uint32_t k_off, double c104) {
+    const uint64_t* kk = f52_pool_u(k_off);
+#pragma unroll
+    for (int k = 0; k < 6; k++) c[k] = kk[k];
+#pragma unroll
+    for (int j = 1; j < T; j++) {
+        const double* tab = f52_pool_d(tw_off + (j - 1) * kF52TabWords);
+#pragma unroll
+        for (int i = 0; i < 5; i++) f52_mac5(c, f52_value(S[j][i]), tab + i * 5, c104);
+    }
+}
+
+// x^alpha, straight-line (no loop, so that it shares a basic block with the FP64 work beside it), lazy
+// form: see sbox_compact<.., LAZY = true> for the bounds.
+template <class F, int ALPHA>
+PSD_DEV void f52_sbox_straight(uint32_t* x) {
+    uint32_t y[8];
+    fp_sqr<F, false>(y, x);
+#pragma unroll
+    for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, false>(y, y);
+    mont_mul<F, false>(x, y, x);
+}
+
+// One full round on the limb state: T S-boxes (lane 0, lanes rotated through it), then T rows.
+template <class F, int T, int ALPHA>
+PSD_DEV void f52_full_round(uint64_t (&S)[T][5], uint32_t mat, uint32_t first_row, uint32_t k_off, const double* consts,
+                            double c104, const PermDesc& d, bool sboxes) {
+    if (sboxes) {
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+        for (uint32_t i = 0; i < T; i++) {
+            uint64_t plain[5];
+#pragma unroll
+            for (int k = 0; k < 5; k++) plain[k] = S[0][k] & kMask52;
+            uint32_t x[8];
+            f52_pack(x, plain);
+            sbox_compact<F, ALPHA, true>(x, d);
+            f52_unpack(S[0], x);
+#pragma unroll
+            for (int k = 0; k < 5; k++) {
+                const uint64_t t0 = S[0][k];
+#pragma unroll
+                for (int l = 0; l + 1 < T; l++) S[l][k] = S[l + 1][k];
+                S[T - 1][k] = t0;
+            }
+        }
+    }
+    // rows first_row..T-1 (rows below first_row keep their lanes: nw starts as a copy shifted in below)
+    uint64_t nw[T][5];
+#pragma unroll
+    for (int l = 0; l < T; l++)
+#pragma unroll
+        for (int k = 0; k < 5; k++) nw[l][k] = 0;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (uint32_t i = first_row; i < T; i++) {
+        uint64_t t[5];
+        const uint32_t off_first = mat + i * T * kF52TabWords;
+        f52_row<T>(t, S, off_first, off_first + kF52TabWords, k_off + (i - first_row) * kF52KWords, consts, c104);
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+#pragma unroll
+            for (int l = 0; l + 1 < T; l++) nw[l][k] = nw[l + 1][k];
+            nw[T - 1][k] = t[k] | kMagicLo;
+        }
+    }
+    // after T - first_row shifts, row i sits in nw[i]; rows below first_row are the caller's business
+#pragma unroll
+    for (int l = 0; l < T; l++)
+#pragma unroll
+        for (int k = 0; k < 5; k++)
+            if (l >= 1 || first_row == 0) S[l][k] = nw[l][k];
+}
+
 template <class F, int T, int ALPHA>
 PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
     static_assert(F::kBits == 254 && (ALPHA == 5 || ALPHA == 17), "variant 5: BN254 Fr, alpha 5 or 17");
@@ -77,7 +156,7 @@ PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
         fp_add<F>(st[j], st[j], c);
         f52_unpack(S[j], st[j]);
     }
-    const uint32_t first_partial = d.half_full, first_post = d.half_full + d.partial;
+    const uint32_t half = d.half_full, rp = d.partial;
     const double* consts = f52_pool_d(d.fp_consts_off);
     // 2^104 must sit in a VECTOR register (see f52_prod); a value the compiler can prove warp-uniform
     // would be kept in a uniform register or folded into an immediate, and either way each product
@@ -88,88 +167,86 @@ PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
 #else
     const double c104 = consts[kF52ConstC104];
 #endif
-    uint32_t k_off = d.fp_k_off, part_off = d.fp_part_off;
+    const uint64_t shift = reinterpret_cast<const uint64_t*>(consts)[kF52ConstShift];
+    uint32_t k_off = d.fp_k_off;
+
+    // full rounds before the partial rounds
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-    for (uint32_t r = 0; r < d.total; r++) {
-        const bool full = (r < first_partial || r >= first_post);
-        const bool all_rows = full || (r + 1 == first_post);      // the last partial round runs T rows
-        const uint32_t n_sbox = full ? T : 1, n_rows = all_rows ? T : 1;
-        const uint32_t mat = full ? ((r + 1 == first_partial && d.partial) ? d.fp_pre_off : d.fp_mat_off)
-                                  : d.fp_last_off;
-        // phase A: S-boxes on lane 0, lanes rotated through it in the full rounds
-#if defined(__CUDACC__)
-#pragma unroll 1
-#endif
-        for (uint32_t i = 0; i < n_sbox; i++) {
+    for (uint32_t r = 0; r < half; r++) {
+        f52_full_round<F, T, ALPHA>(S, (r + 1 == half && rp) ? d.fp_pre_off : d.fp_mat_off, 0, k_off, consts, c104, d, true);
+        k_off += T * kF52KWords;
+    }
+
+    if (rp) {
+        // Partial rounds.  Only lane 0's chain  S-box -> row 0 -> S-box  is serial; the lane updates of
+        // round i and the lanes' share of row 0 of round i+1 depend on nothing the S-box of round i+1
+        // produces, so they are written next to it; the S-box output's share of the row and the two
+        // Montgomery rows follow once the S-box is done.
+        uint32_t part_off = d.fp_part_off;
+        uint32_t x[8];
+        {
             uint64_t plain[5];
 #pragma unroll
             for (int k = 0; k < 5; k++) plain[k] = S[0][k] & kMask52;
-            uint32_t x[8];
             f52_pack(x, plain);
-            sbox_compact<F, ALPHA, true>(x, d);
-            f52_unpack(S[0], x);
-            if (full) {
-#pragma unroll
-                for (int k = 0; k < 5; k++) {
-                    const uint64_t t0 = S[0][k];
-#pragma unroll
-                    for (int l = 0; l + 1 < T; l++) S[l][k] = S[l + 1][k];
-                    S[T - 1][k] = t0;
-                }
-            }
         }
-        // phase B: rows
-        uint64_t nw[T][5];
-#pragma unroll
-        for (int l = 0; l < T; l++)
-#pragma unroll
-            for (int k = 0; k < 5; k++) nw[l][k] = 0;
+        uint64_t c[6];
+        f52_sbox_straight<F, ALPHA>(x);
+        f52_row_lanes<T>(c, S, part_off, k_off, c104);
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-        for (uint32_t i = 0; i < n_rows; i++) {
-            uint64_t t[5];
-            const uint32_t off_first = all_rows ? mat + i * T * kF52TabWords : d.fp_mat_off;
-            const uint32_t off_rest = all_rows ? off_first + kF52TabWords : part_off;
-            f52_row<T>(t, S, off_first, off_rest, k_off, consts, c104);
-            k_off += kF52KWords;
-#pragma unroll
-            for (int k = 0; k < 5; k++) {
-#pragma unroll
-                for (int l = 0; l + 1 < T; l++) nw[l][k] = nw[l + 1][k];
-                nw[T - 1][k] = t[k] | kMagicLo;
-            }
-        }
-        if (all_rows) {
-#pragma unroll
-            for (int l = 0; l < T; l++)
-#pragma unroll
-                for (int k = 0; k < 5; k++) S[l][k] = nw[l][k];
-        } else {
-            // phase C: lane updates with y = S[0]
+        for (uint32_t i = 0;; i++) {
+            // finish row 0 of partial round i: the S-box output's share, two Montgomery rows
+            f52_unpack(S[0], x);
             double y[5];
 #pragma unroll
             for (int k = 0; k < 5; k++) y[k] = f52_value(S[0][k]);
+            {
+                const double* tab = f52_pool_d(d.fp_mat_off);
+#pragma unroll
+                for (int l = 0; l < 5; l++) f52_mac5(c, y[l], tab + l * 5, c104);
+            }
+            f52_mont_row(c, consts, shift, c104);
+            f52_mont_row(c, consts, shift, c104);
+            f52_normalise(c);
+            k_off += kF52KWords;
+            if (i + 1 == rp) break;
+            f52_pack(x, c);
+            // S-box of round i+1  ||  lane updates of round i, lane part of row 0 of round i+1: one
+            // straight-line block.  Measured on B200 (c2): 163.1 M perm/s, against 162.2 M for rolled
+            // phases in program order and 151-157 M for a rolled lane loop next to a rolled S-box, even
+            // though this body (1.5 K instructions) misses the instruction cache (ncu: no_instruction
+            // is 18 % of the stall samples).
+            f52_sbox_straight<F, ALPHA>(x);
+#pragma unroll
+            for (int j = 1; j < T; j++)
+                f52_lane_update(S[j], y, part_off + (T - 1 + j - 1) * kF52TabWords, consts, c104);
+            part_off += 2 * (T - 1) * kF52TabWords;
+            f52_row_lanes<T>(c, S, part_off, k_off, c104);
+        }
+        // last partial round: lanes 1..T-1 come from rows of the `last` matrix (lane update + rescale),
+        // lane 0 is the row just finished
+        uint64_t lane0[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) lane0[k] = c[k] | kMagicLo;
+        f52_full_round<F, T, ALPHA>(S, d.fp_last_off, 1, k_off, consts, c104, d, false);
+        k_off += (T - 1) * kF52KWords;
+#pragma unroll
+        for (int k = 0; k < 5; k++) S[0][k] = lane0[k];
+    }
+
+    // full rounds after the partial rounds
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-            for (uint32_t j = 0; j + 1 < T; j++) {
-                f52_lane_update(S[1], y, part_off + (T - 1 + j) * kF52TabWords, consts, c104);
-#pragma unroll
-                for (int k = 0; k < 5; k++) {
-                    const uint64_t t1 = S[1][k];
-#pragma unroll
-                    for (int l = 1; l + 1 < T; l++) S[l][k] = S[l + 1][k];
-                    S[T - 1][k] = t1;
-                }
-            }
-            part_off += 2 * (T - 1) * kF52TabWords;
-#pragma unroll
-            for (int k = 0; k < 5; k++) S[0][k] = nw[T - 1][k];
-        }
+    for (uint32_t r = half + rp; r < d.total; r++) {
+        f52_full_round<F, T, ALPHA>(S, d.fp_mat_off, 0, k_off, consts, c104, d, true);
+        k_off += T * kF52KWords;
     }
+
     // back to canonical 8 x 32-bit residues (rows leave values < p + 2^207)
 #pragma unroll
     for (int j = 0; j < T; j++) {
