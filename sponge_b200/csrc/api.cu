@@ -247,9 +247,19 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
     // the permutation and the multiplier pipe stays fed), and the kernel has no per-thread loop so
     // that ptxas keeps round constants on the uniform datapath.
     (void)ctx;
-    (void)k;
     LaunchCfg cfg;
     cfg.block = 128;
+    if (k->variant == 5) {
+        // Variant 5's partial-round body (1.5 K instructions) does not fit the instruction caches when
+        // the warps of a scheduler sit at different places in it.  Warps of ONE block start together and
+        // stay close, so large blocks share their instruction fetches: measured on B200 (c2) 162.8 M
+        // perm/s with 128-thread blocks, 172.9 M with 256, 175.0 M with 512 (one 128-register block per
+        // SM).  Small batches keep smaller blocks so that every SM still gets one.
+        const uint64_t sms = (uint64_t)std::max(1, ctx->sm_count);
+        cfg.block = n >= 512 * sms ? 512 : n >= 256 * sms ? 256 : 128;
+        const int forced = env_int("PSD_FP52_BLOCK", 0);   // tuning runs
+        if (forced >= 32 && forced <= 512 && forced % 32 == 0) cfg.block = forced;
+    }
     cfg.grid = (int)std::max<uint64_t>(1, (n + cfg.block - 1) / cfg.block);
     return cfg;
 }
@@ -381,9 +391,11 @@ psd_status run_staged(psd_ctx* ctx, const StagedCall& c, Fill fill) {
     const size_t out_per = c.out_bytes_per ? c.out_bytes_per : (size_t)c.out_w * 32;
     // chunk: 2^16 sponges.  Three chunks in flight (one per stream) keep all SMs busy, and short chunks
     // shrink the un-overlapped first upload / last download: measured on C2 (2^24 states from pinned
-    // memory) 2^16 -> 99.8 % of the device-resident rate, 2^20 -> 97.3 %.
+    // memory) 2^16 -> 99.8 % of the device-resident rate, 2^20 -> 97.3 %.  With variant 5, whose large
+    // blocks want at least 512 sponges per SM in a launch, 2^17 is the better chunk (172.4 M perm/s end
+    // to end at 2^16, 174.4 M at 2^17, 173.6 M at 2^18, against 175.1 M device-resident).
     const size_t per = std::max<size_t>(1, in_per + (c.in_place ? 0 : out_per));
-    static const int chunk_log2 = env_int("PSD_STAGE_CHUNK_LOG2", 16);   // development knob
+    static const int chunk_log2 = env_int("PSD_STAGE_CHUNK_LOG2", 17);   // development knob
     uint64_t chunk = std::max<uint64_t>((256ull << 20) / per, 1ull << 16);
     chunk = std::min<uint64_t>(chunk, 1ull << chunk_log2);
     chunk = std::min<uint64_t>(chunk, c.n);

@@ -83,8 +83,12 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #endif
 #define PSD_KERNEL_MIN_BLOCKS(T, VARIANT) ((VARIANT) == 5 ? PSD_MIN_BLOCKS_FP52 : PSD_MIN_BLOCKS(T))
 
+// variant 5 may be launched with up to 512 threads per block (one block of 128 registers per thread
+// fills an SM); every other variant runs 128-thread blocks
+#define PSD_KERNEL_MAX_BLOCK(VARIANT) ((VARIANT) == 5 ? 512 : 128)
+#define PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT) ((VARIANT) == 5 ? 1 : PSD_MIN_BLOCKS(T))
 template <class F, int T, int ALPHA, int VARIANT>
-__global__ void __launch_bounds__(128, PSD_KERNEL_MIN_BLOCKS(T, VARIANT)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+__global__ void __launch_bounds__(PSD_KERNEL_MAX_BLOCK(VARIANT), PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
     const PermDesc& d = a.d;
     const uint32_t rate = d.rate, cap = d.capacity;
     bool bad = false;
