@@ -443,16 +443,30 @@ def main():
     # of that on B200 (k0.imad_wide_per_s), so a kernel that executes all W_alg multiplies as IMAD.WIDE
     # tops out near 0.45; the optimised kernel gets above that by executing fewer multiplies than W_alg.
     # DRAM bytes per launch from the committed ncu --set full capture of this exact workload
-    # (profiles/r1_c2_final_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
-    traffic = 3.195e9 if (name == "c2" and log_n == 24) else None
+    # (profiles/r1c_c2_v5_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
+    traffic = 3.196e9 if (name == "c2" and log_n == 24) else None
+    active_variant = ctx.active_variant()
+    # Executed work and pipe activity of the kernel that ran, for c2, from the committed ncu captures:
+    #   variant 5 (profiles/r1c_c2_v5_summary.md): integer multiplies only in the S-boxes and the Montgomery
+    #   quotient digits; the linear layer is 10 415 exact 52x52-bit products on the FP64 pipe (3 FP64
+    #   instructions each).  The three pipes overlap little on B200.
+    #   variant 3 (profiles/r1_c2_final_summary.md): all-integer, 56 625 multiplies, fmaheavy 89.5 % active.
+    if name == "c2" and active_variant == 5:
+        exec_info = dict(w_exec_imul_per_perm=29346, fp64_products_per_perm=10415, fmaheavy_active_pct_ncu=54.5,
+                         fp64_active_pct_ncu=30.7, alu_active_pct_ncu=40.4, issue_active_pct_ncu=55.1)
+    elif name == "c2" and active_variant == 3:
+        exec_info = dict(w_exec_imul_per_perm=56625, fp64_products_per_perm=0, fmaheavy_active_pct_ncu=89.5,
+                         fp64_active_pct_ncu=0.0, alu_active_pct_ncu=38.2, issue_active_pct_ncu=47.8)
+    else:
+        exec_info = dict(w_exec_imul_per_perm=None, fmaheavy_active_pct_ncu=None)
     roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_lo / 1e9, unit="Gimul/s",
                     frac=achieved_imul / imad_lo, traffic=traffic,
                     w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
-                    # executed multiplies and multiplier-pipe activity of the shipped kernel for this workload, from
-                    # the committed ncu capture (profiles/r1_c2_final_summary.md); W_exec < W_alg because of
-                    # sparse partial rounds, digit-table constant products and dedicated squaring
-                    w_exec_imul_per_perm=(56625 if name == "c2" else None),
-                    fmaheavy_active_pct_ncu=(89.5 if name == "c2" else None),
+                    # achieved = ALGORITHMIC multiplies (the reference's operation count) per
+                    # second; the shipped kernels execute fewer (sparse partial rounds, constant products through
+                    # tables, dedicated squaring), which is how frac can pass the 0.5 that
+                    # IMAD.WIDE's half rate would otherwise impose
+                    **exec_info,
                     peak_source="K0 probe in this run: sustained 32-bit IMAD results/s on all SMs "
                                 "(integer-multiply pipe issue rate)",
                     k0=dict(imad_wide_per_s=imad_wide, imad_lo_per_s=imad_lo, mont_mul_per_s=modmul_rate,

@@ -155,6 +155,74 @@ __global__ void __launch_bounds__(128) k_sbox_fp(uint64_t* out, uint32_t iters) 
     if (s == 0x123456789ull) out[0] = s;
 }
 
+// (f) cross-warp overlap: blocks of 256 threads (2 warps per SMSP); warps 0-3 run S-boxes, warps 4-7
+// run table products (register operands), SPLIT = 0: every warp does both, one after the other
+template <int SPLIT>
+__global__ void __launch_bounds__(256) k_mixed(uint64_t* out, uint32_t iters) {
+    const double c104 = opaque104();
+    uint32_t x[8];
+    for (int i = 0; i < 8; i++) x[i] = (uint32_t)out[(threadIdx.x + i) & 63] >> (i == 7 ? 3 : 0);
+    double a[5], b[5];
+    for (int i = 0; i < 5; i++) {
+        a[i] = (double)((threadIdx.x * 977u + i * 131u) & 0xfffff);
+        b[i] = (double)(out[(threadIdx.x + i) & 63] >> 13);
+    }
+    uint64_t c[6] = {0, 0, 0, 0, 0, 0};
+    const bool do_int = SPLIT ? (threadIdx.x < 128) : true, do_fp = SPLIT ? (threadIdx.x >= 128) : true;
+    // per iteration: 2 S-boxes or 8 x 25 products when split, 1 S-box + 4 x 25 products when not:
+    // the same total work per block either way
+    const int n_int = SPLIT ? 2 : 1, n_fp = SPLIT ? 8 : 4;
+#pragma unroll 1
+    for (uint32_t it = 0; it < iters; it++) {
+        if (do_int) {
+#pragma unroll 1
+            for (int r = 0; r < n_int; r++) {
+                f52_sbox_straight<Bn254Fr, 5>(x);
+                x[7] &= 0x1fffffffu;
+            }
+        }
+        if (do_fp) {
+#pragma unroll 1
+            for (int r = 0; r < n_fp; r++) {
+#pragma unroll
+                for (int i = 0; i < 5; i++) {
+                    uint64_t hi[5], lo[5];
+#pragma unroll
+                    for (int k = 0; k < 5; k++) f52_prod(hi[k], lo[k], a[i], b[k], c104);
+                    c[0] += lo[0];
+#pragma unroll
+                    for (int k = 1; k < 5; k++) c[k] += lo[k] + hi[k - 1];
+                    c[5] += hi[4];
+                }
+#pragma unroll
+                for (int i = 0; i < 5; i++) a[i] = __longlong_as_double(__double_as_longlong(a[i]) ^ 0x100ll);
+            }
+        }
+    }
+    uint64_t s = 0;
+    for (int i = 0; i < 8; i++) s ^= x[i];
+    for (int k = 0; k < 6; k++) s ^= c[k];
+    if (s == 0x123456789ull) out[0] = s;
+}
+
+template <class K>
+static void run256(const char* name, K kern, int blocks_per_sm, uint32_t iters, uint64_t* d, int sms, double clk_mhz) {
+    kern<<<sms * blocks_per_sm, 256>>>(d, 16);
+    cudaDeviceSynchronize();
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0);
+    kern<<<sms * blocks_per_sm, 256>>>(d, iters);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double cyc = ms * 1e-3 * clk_mhz * 1e6;
+    printf("%-34s blocks/SM=%d  %8.3f ms  SMSP cycles per (1 S-box + 100 products) = %8.1f   [%s]\n", name,
+           blocks_per_sm, ms, cyc / iters / blocks_per_sm / 2, cudaGetErrorString(cudaGetLastError()));
+}
+
 template <class K>
 static void run(const char* name, K kern, int blocks_per_sm, uint32_t iters, uint64_t* d, int sms, double clk_mhz) {
     const int block = 128;   // 1 warp per SMSP per block
@@ -198,5 +266,7 @@ int main() {
     for (int w : {1, 4}) run("25x 3-input 64-bit adds (+20 ALU)", k_alu_only, w, it, d, sms, clk);
     for (int w : {1, 2, 4, 6}) run("integer S-box x^5 (lazy)", k_sbox, w, it, d, sms, clk);
     for (int w : {4}) run("S-box + 50 products, one block", k_sbox_fp<2>, w, it, d, sms, clk);
+    for (int w : {1, 2, 3}) run256("every warp: S-box then products", k_mixed<0>, w, it, d, sms, clk);
+    for (int w : {1, 2, 3}) run256("half the warps each", k_mixed<1>, w, it, d, sms, clk);
     return 0;
 }
