@@ -75,16 +75,11 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #define PSD_MIN_BLOCKS(T) ((T) <= 3 ? 7 : (T) == 5 ? 5 : 0)   /* 0 = no hint; t=5: 83.8 M vs 83.0 M hash/s */
 #endif
 // Variant 5 keeps the state in 52-bit limb pairs next to the integer S-box temporaries, and its partial
-// rounds hold an S-box and two lane updates in one block: 128 registers, 4 resident blocks.
-// Measured on B200 (c2): 163.1 M perm/s at 4 blocks; 147.3 M at 5 (96 registers, spills).  Not
-// occupancy-limited: the form with rolled phases ran 162 M at 5, 6 and 7 blocks alike.
-#ifndef PSD_MIN_BLOCKS_FP52
-#define PSD_MIN_BLOCKS_FP52 4
-#endif
-#define PSD_KERNEL_MIN_BLOCKS(T, VARIANT) ((VARIANT) == 5 ? PSD_MIN_BLOCKS_FP52 : PSD_MIN_BLOCKS(T))
-
-// variant 5 may be launched with up to 512 threads per block (one block of 128 registers per thread
-// fills an SM); every other variant runs 128-thread blocks
+// rounds hold an S-box and two lane updates in one block: 128 registers per thread.  It may be launched
+// with up to 512 threads per block (one such block fills an SM, see sponge_cfg in api.cu); every other
+// variant runs 128-thread blocks.  Measured on B200 (c2, 128-thread blocks): 163.1 M perm/s at 128
+// registers, 147.3 M when capped at 96 (spills); not occupancy-limited -- the form with rolled phases
+// ran 162 M at 5, 6 and 7 resident blocks alike.
 #define PSD_KERNEL_MAX_BLOCK(VARIANT) ((VARIANT) == 5 ? 512 : 128)
 #define PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT) ((VARIANT) == 5 ? 1 : PSD_MIN_BLOCKS(T))
 template <class F, int T, int ALPHA, int VARIANT>

@@ -53,6 +53,20 @@ def test_fp52_permute_matches_oracle(S, ref, name):
         ctx.close()
 
 
+@pytest.mark.parametrize("n", [40000, 80000, 80001])
+def test_fp52_large_blocks_match_oracle(S, ref, n):
+    """Batches large enough for the 256- and 512-thread block launches (more than 256 / 512 sponges per
+    SM), with a ragged last block, against the oracle element for element."""
+    oc, orc, ctx = make(S, ref, "bn254_t3")
+    try:
+        assert ctx.active_variant() == 5          # the default for the first eligible context
+        t = oc.rate + oc.capacity
+        st = orc.synth(n * t, seed=0xB10C + n, montgomery=True)
+        assert np.array_equal(ctx.permute_batch(st.copy()), orc.permute_batch(st.copy()))
+    finally:
+        ctx.close()
+
+
 def test_fp52_sponge_calls(S, ref):
     """absorb/squeeze sequences and the Merkle driver run on the same kernel."""
     oc, orc, ctx = make(S, ref, "bn254_t3")
