@@ -87,7 +87,6 @@ void append_fp52_tables(const HostField& f, uint32_t t, uint32_t full_rounds, ui
                         std::vector<uint32_t>& img) {
     d.fp_ok = 0;
     d.fp_consts_off = d.fp_mat_off = d.fp_pre_off = d.fp_last_off = d.fp_k_off = d.fp_part_off = 0;
-    if (f.bits != 254) return;   // the lazy integer S-box this variant pairs with needs 5.29 p > 2^256
     const uint32_t half = full_rounds / 2, rp = partial_rounds, n = t - 1, total = full_rounds + rp;
     if (half == 0 || full_rounds - half == 0) return;
 

@@ -11,7 +11,9 @@
 // 1..T-1 hold s_j * sigma_i with sigma_i = 2^(-52 i) after i lane updates; the host scales the tables
 // of partial round i accordingly (w_j / sigma_i, v_j * sigma_i), and the last partial round is run as
 // T full rows whose matrix also undoes the scale, so the full rounds never see it.
-// Bounds (5-limb values): lanes < 2^258 stay < 2^206 + 6p < 2^258; every limb < 2^52 after normalising.
+// Bounds (5-limb values): lanes < 2^258 stay < 2^206 + 6p < 2^258 (6p = 1.13 * 2^256 for BN254, 2.72 * 2^256 for
+// BLS12-381); every limb < 2^52 after normalising.  For BLS12-381 the S-box input is brought below p first
+// (one conditional subtraction) and the S-box keeps its reductions.
 #pragma once
 #include "fp52.cuh"
 
@@ -80,15 +82,35 @@ PSD_DEV void f52_row_lanes(uint64_t* c, const uint64_t (*S)[5], uint32_t tw_off,
     }
 }
 
-// x^alpha, straight-line (no loop, so that it shares a basic block with the FP64 work beside it), lazy
-// form: see sbox_compact<.., LAZY = true> for the bounds.
+// Which fields may skip the conditional subtractions inside x^alpha (see sbox_compact<.., LAZY>): BN254
+// (5.29 p > 2^256).  BLS12-381 (2p > 2^255, and its squaring folds a to min(a, p-a)) needs canonical
+// S-box inputs and produces canonical outputs.
+template <class F>
+struct F52Lazy {
+    static constexpr bool value = (F::kBits == 254);
+};
+
+// x (five plain limbs, value < p + 2^207) -> S-box input words
+template <class F>
+PSD_DEV void f52_pack_sbox_input(uint32_t* x, const uint64_t* plain) {
+    if (F52Lazy<F>::value) {
+        f52_pack(x, plain);
+    } else {
+        uint32_t w[8];
+        f52_pack(w, plain);
+        cond_sub_p<F>(x, w);
+    }
+}
+
+// x^alpha, straight-line (no loop, so that it shares a basic block with the FP64 work beside it)
 template <class F, int ALPHA>
 PSD_DEV void f52_sbox_straight(uint32_t* x) {
+    constexpr bool kReduce = !F52Lazy<F>::value;
     uint32_t y[8];
-    fp_sqr<F, false>(y, x);
+    fp_sqr<F, kReduce>(y, x);
 #pragma unroll
-    for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, false>(y, y);
-    mont_mul<F, false>(x, y, x);
+    for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, kReduce>(y, y);
+    mont_mul<F, kReduce>(x, y, x);
 }
 
 // One full round on the limb state: T S-boxes (lane 0, lanes rotated through it), then T rows.
@@ -104,8 +126,8 @@ PSD_DEV void f52_full_round(uint64_t (&S)[T][5], uint32_t mat, uint32_t first_ro
 #pragma unroll
             for (int k = 0; k < 5; k++) plain[k] = S[0][k] & kMask52;
             uint32_t x[8];
-            f52_pack(x, plain);
-            sbox_compact<F, ALPHA, true>(x, d);
+            f52_pack_sbox_input<F>(x, plain);
+            sbox_compact<F, ALPHA, F52Lazy<F>::value>(x, d);
             f52_unpack(S[0], x);
 #pragma unroll
             for (int k = 0; k < 5; k++) {
@@ -146,7 +168,7 @@ PSD_DEV void f52_full_round(uint64_t (&S)[T][5], uint32_t mat, uint32_t first_ro
 
 template <class F, int T, int ALPHA>
 PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
-    static_assert(F::kBits == 254 && (ALPHA == 5 || ALPHA == 17), "variant 5: BN254 Fr, alpha 5 or 17");
+    static_assert(ALPHA == 5 || ALPHA == 17, "variant 5: alpha 5 or 17");
     uint64_t S[T][5];
     // round-0 constants on the integer side, then into limb form
 #pragma unroll
@@ -190,7 +212,7 @@ PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
             uint64_t plain[5];
 #pragma unroll
             for (int k = 0; k < 5; k++) plain[k] = S[0][k] & kMask52;
-            f52_pack(x, plain);
+            f52_pack_sbox_input<F>(x, plain);
         }
         uint64_t c[6];
         f52_sbox_straight<F, ALPHA>(x);
@@ -214,7 +236,7 @@ PSD_DEV void permute_fp52(uint32_t (&st)[T][8], const PermDesc& d) {
             f52_normalise(c);
             k_off += kF52KWords;
             if (i + 1 == rp) break;
-            f52_pack(x, c);
+            f52_pack_sbox_input<F>(x, c);
             // S-box of round i+1  ||  lane updates of round i, lane part of row 0 of round i+1: one
             // straight-line block.  Measured on B200 (c2): 163.1 M perm/s, against 162.2 M for rolled
             // phases in program order and 151-157 M for a rolled lane loop next to a rolled S-box, even

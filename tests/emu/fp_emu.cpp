@@ -54,10 +54,10 @@ extern "C" void emu_mont_dot(int n_terms, uint32_t* r, const uint32_t* a, const 
 #include "../../sponge_b200/csrc/poseidon_core.cuh"
 #include "../../sponge_b200/csrc/poseidon_fp52.cuh"
 
-// the FP64-pipe variant exists for BN254 Fr with alpha 5 / 17 only
+// the FP64-pipe variant exists for alpha 5 / 17 only
 template <class F, int T, int ALPHA>
 static bool emu_perm_fp52(uint32_t (&s)[T][8], const PermDesc& d) {
-    if constexpr (F::kBits == 254 && (ALPHA == 5 || ALPHA == 17) && T <= 5) {
+    if constexpr ((ALPHA == 5 || ALPHA == 17) && T <= 5) {
         permute_fp52<F, T, ALPHA>(s, d);
         return true;
     } else {
@@ -135,7 +135,7 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
                         : emu_perm_f<Bls12381Fr>(d, t, alpha, variant, states, n);
     fesetround(old_round);
     if (rc) return rc;
-    if (variant == 6 && !(d.fp_ok && field == 0 && (alpha == 5 || alpha == 17) && t <= 5)) return 1;
+    if (variant == 6 && !(d.fp_ok && (alpha == 5 || alpha == 17) && t <= 5)) return 1;
     if ((variant == 4 && d.ctab_ok != 1) || (variant == 5 && d.ctab_ok != 2)) return 1;
     return ((variant == 1 || variant == 3) && !d.opt_ok) ? 1 : 0;
 }
