@@ -614,7 +614,7 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->pool_held = true;
     offset_desc(ctx->desc, ctx->pool_off);
 
-    // Variant 5 (FP64-pipe linear layer): its own image [ark][mds][one][r2][52-bit-limb tables] in the
+    // Variant 5 (FP64-pipe linear layer): its own image [ark of round 0][mds][one][r2][52-bit-limb tables] in the
     // pool of tu_fp52.cu, for the parameter sets that unit has kernels for, when that pool has room
     // (one parameter set nearly fills it, so in practice the first live context gets it).
     std::vector<uint32_t> fimg;
@@ -624,7 +624,14 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
             PermDesc fd = base_desc;
             fd.opt_ok = fd.ctab_ok = 0;
             fd.pre_mds_off = fd.sparse_off = fd.post_ark_off = 0;
-            fimg.assign(img.begin(), img.begin() + base_desc.r2_off + 8);   // [ark][mds][one][r2]
+            // [ark of round 0][mds][one][r2]: the later round constants are inside the tables
+            fimg.assign(img.begin(), img.begin() + t * 8);
+            fd.mds_off = (uint32_t)fimg.size();
+            fimg.insert(fimg.end(), img.begin() + base_desc.mds_off, img.begin() + base_desc.mds_off + t * t * 8);
+            fd.one_off = (uint32_t)fimg.size();
+            fimg.insert(fimg.end(), img.begin() + base_desc.one_off, img.begin() + base_desc.one_off + 8);
+            fd.r2_off = (uint32_t)fimg.size();
+            fimg.insert(fimg.end(), img.begin() + base_desc.r2_off, img.begin() + base_desc.r2_off + 8);
             append_fp52_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, fd, fimg);
             if (fd.fp_ok && fimg.size() <= kConstPoolWords &&
                 pool_alloc(device, p->field, kFp52PoolKey, (uint32_t)fimg.size(), &ctx->fpool_off, nullptr)) {

@@ -113,7 +113,8 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     };
     PermDesc d{};
     d.ark_off = 0;
-    for (auto& f : ark) push(f);
+    // variant 6 only reads the round-0 constants from here (as the library's variant-5 image does)
+    for (size_t i = 0; i < (variant == 6 ? (size_t)t : ark.size()); i++) push(ark[i]);
     d.mds_off = (uint32_t)img.size();
     for (auto& f : mds) push(f);
     d.one_off = (uint32_t)img.size();
