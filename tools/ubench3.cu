@@ -91,6 +91,34 @@ __global__ void __launch_bounds__(128) k_fp_reg(uint64_t* out, uint32_t iters) {
     if (x == 0x123456789ull) out[0] = x;
 }
 
+// (a3) FP64 instruction mixes, register operands, 100 instructions per iteration in 25 independent
+// chains of 4:  MIX 0: fma.rz only; 1: fma.rn only; 2: add.rz only; 3: fma.rz, add.rz alternating;
+// 4: fma.rz with the subtraction done as a second fma (hi * -1 + C2)
+template <int MIX>
+__global__ void __launch_bounds__(128) k_fp64_mix(uint64_t* out, uint32_t iters) {
+    double v[25], b = (double)(out[threadIdx.x & 63] >> 13), c2 = 20282409603651674927546878656512.0;
+    for (int i = 0; i < 25; i++) v[i] = (double)((threadIdx.x * 977u + i * 131u) & 0xfffff);
+#pragma unroll 1
+    for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 25; i++) {
+            double x = v[i];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (MIX == 0) x = __fma_rz(x, b, c2);
+                else if (MIX == 1) x = __fma_rn(x, b, c2);
+                else if (MIX == 2) x = __dadd_rz(x, b);
+                else if (MIX == 3) x = (q & 1) ? __dadd_rz(c2, -x) : __fma_rz(x, b, c2);
+                else x = (q & 1) ? __fma_rz(x, -1.0, c2) : __fma_rz(x, b, c2);
+            }
+            v[i] = x;
+        }
+    }
+    double s = 0;
+    for (int i = 0; i < 25; i++) s += v[i];
+    if (s == 1.2345) out[0] = 1;
+}
+
 // (c) the accumulation of (a) only: 25 three-input 64-bit adds per iteration on register values
 __global__ void __launch_bounds__(128) k_alu_only(uint64_t* out, uint32_t iters) {
     uint64_t v[10];
@@ -258,6 +286,11 @@ int main() {
     for (int i = 0; i < 512; i++) h[i] = 0x9e3779b97f4a7c15ull * (i + 3);
     cudaMemcpy(d, h.data(), 4096, cudaMemcpyHostToDevice);
     const uint32_t it = 4096;
+    for (int w : {4, 8}) run("100 x fma.rz", k_fp64_mix<0>, w, it, d, sms, clk);
+    for (int w : {4, 8}) run("100 x fma.rn", k_fp64_mix<1>, w, it, d, sms, clk);
+    for (int w : {4, 8}) run("100 x add.rz", k_fp64_mix<2>, w, it, d, sms, clk);
+    for (int w : {4, 8}) run("50 fma.rz + 50 add.rz", k_fp64_mix<3>, w, it, d, sms, clk);
+    for (int w : {4, 8}) run("100 x fma.rz (sub as fma)", k_fp64_mix<4>, w, it, d, sms, clk);
     for (int w : {1, 2, 4, 6}) run("25 products + int acc, registers", k_fp_reg<1>, w, it, d, sms, clk);
     for (int w : {1, 2, 4, 6}) run("25 products + FP acc, registers", k_fp_reg<0>, w, it, d, sms, clk);
     for (int w : {1, 4, 6}) run("25 products + acc, uniform loads", k_fp_full<1>, w, it, d, sms, clk);
