@@ -216,3 +216,28 @@ extern "C" void emu_const_dot(int field, int n_terms, uint32_t* r, const uint32_
 #undef PSD_CASE
     }
 }
+
+// ---- fp52.cuh primitives (FP64-pipe products), under round-toward-zero as on the device -------------
+extern "C" void emu_f52_prod(const uint64_t* a, const uint64_t* b, uint64_t* hi, uint64_t* lo, size_t n) {
+    const int old_round = fegetround();
+    fesetround(FE_TOWARDZERO);
+    for (size_t i = 0; i < n; i++) {
+        uint64_t h, l;
+        f52_prod(h, l, (double)a[i], (double)b[i], 20282409603651670423947251286016.0);
+        hi[i] = h - kMagicHi;
+        lo[i] = l - kMagicLo;
+    }
+    fesetround(old_round);
+}
+// 8 x 32-bit words -> five limbs -> 8 x 32-bit words
+extern "C" void emu_f52_unpack_pack(const uint32_t* x, uint64_t* limbs, uint32_t* back, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        uint64_t m[5];
+        f52_unpack(m, x + 8 * i);
+        for (int k = 0; k < 5; k++) limbs[5 * i + k] = m[k] - kMagicLo;
+        uint64_t plain[5];
+        for (int k = 0; k < 5; k++) plain[k] = m[k] & kMask52;
+        f52_pack(back + 8 * i, plain);
+    }
+}
+

@@ -182,6 +182,7 @@ def test_permutation_variants_host_model(emu, ref, name):
     n = 24
     st = orc.synth(n * t, seed=5)
     st[:t] = 0
+    st[t:2 * t] = to_limbs([cfg.p - 1] * t)      # largest residues in every lane
     exp = orc.permute_batch(st.copy())
     ark = to_limbs(v for r in cfg.ark for v in r)
     mds = to_limbs(v for r in cfg.mds for v in r)
@@ -296,3 +297,34 @@ def test_squaring_and_wide_window_host_model(emu, ref, field):
         emu.emu_mont_dot_w(field, n_terms, C.c_void_p(r.ctypes.data), C.c_void_p(av.ctypes.data),
                            C.c_void_p(bv.ctypes.data), C.c_size_t(m))
         assert to_ints(r.view(np.uint64)) == [sum(x * y for x, y in zip(ra, rb)) * rinv % p for ra, rb in zip(AA, BB)]
+
+
+def test_fp52_primitives_host_model(emu):
+    """fp52.cuh: the two-FMA exact product (round toward zero) and the 52-bit limb packing, on extreme and
+    random operands, against Python integers."""
+    rng = random.Random(52)
+    top = (1 << 52) - 1
+    edge = [0, 1, 2, top, top - 1, 1 << 51, (1 << 51) - 1, (1 << 26) - 1, 1 << 26, 0xfffff00000000, 0xfffffffff]
+    A = [x for x in edge for _ in edge] + [rng.randrange(1 << 52) for _ in range(20000)]
+    B = [y for _ in edge for y in edge] + [rng.randrange(1 << 52) for _ in range(20000)]
+    n = len(A)
+    a = np.array(A, dtype=np.uint64)
+    b = np.array(B, dtype=np.uint64)
+    hi = np.zeros(n, dtype=np.uint64)
+    lo = np.zeros(n, dtype=np.uint64)
+    emu.emu_f52_prod(C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(hi.ctypes.data),
+                     C.c_void_p(lo.ctypes.data), C.c_size_t(n))
+    for x, y, h, l in zip(A, B, hi.tolist(), lo.tolist()):
+        assert (h << 52) + l == x * y and l < (1 << 52)
+    vals = [0, 1, (1 << 256) - 1, (1 << 52) - 1, 1 << 52, (1 << 104) - 1, 1 << 208, (1 << 208) - 1] + \
+           [rng.randrange(1 << 256) for _ in range(2000)]
+    x = to_limbs(vals).view(np.uint32)
+    limbs = np.zeros(5 * len(vals), dtype=np.uint64)
+    back = np.zeros_like(x)
+    emu.emu_f52_unpack_pack(C.c_void_p(x.ctypes.data), C.c_void_p(limbs.ctypes.data), C.c_void_p(back.ctypes.data),
+                            C.c_size_t(len(vals)))
+    assert np.array_equal(back, x)
+    lm = limbs.reshape(-1, 5).tolist()
+    for v, row in zip(vals, lm):
+        assert all(r < (1 << 52) for r in row[:4]) and sum(r << (52 * k) for k, r in enumerate(row)) == v
+
