@@ -9,13 +9,16 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liboracle.so")
+# PSD_SANITIZE=1 (tests/test_sanitizers.py) selects an ASan + UBSan build of the same source
+_SAN = os.environ.get("PSD_SANITIZE") == "1"
+LIB_PATH = os.path.join(_HERE, "liboracle_san.so" if _SAN else "liboracle.so")
 SRC_PATH = os.path.join(_HERE, "poseidon_oracle.c")
 
 
 def build(force: bool = False) -> str:
     if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(SRC_PATH):
-        subprocess.check_call(["gcc", "-O3", "-fopenmp", "-shared", "-fPIC", "-o", LIB_PATH, SRC_PATH])
+        flags = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all"] if _SAN else ["-O3"]
+        subprocess.check_call(["gcc"] + flags + ["-fopenmp", "-shared", "-fPIC", "-o", LIB_PATH, SRC_PATH])
     return LIB_PATH
 
 

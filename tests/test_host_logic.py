@@ -125,7 +125,9 @@ def test_limb_helpers_and_enums(S):
 
 @pytest.fixture(scope="module")
 def emu():
-    so = os.path.join(ROOT, "tests", "emu", "libfp_emu.so")
+    # PSD_SANITIZE=1 (tests/test_sanitizers.py): the same host model built with ASan + UBSan
+    san = os.environ.get("PSD_SANITIZE") == "1"
+    so = os.path.join(ROOT, "tests", "emu", "libfp_emu_san.so" if san else "libfp_emu.so")
     csrc = os.path.join(ROOT, "sponge_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "emu", "fp_emu.cpp"), os.path.join(csrc, "opt_constants.cpp"),
             os.path.join(csrc, "fp52_tables.cpp"),
@@ -135,9 +137,25 @@ def emu():
                                                    "fp52_tables.hpp")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
         # -frounding-math: fp52.cuh's host model runs fma() under FE_TOWARDZERO
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-frounding-math", "-ffp-contract=off", "-shared", "-fPIC",
+        flags = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all"] if san else ["-O2"]
+        subprocess.check_call(["g++"] + flags + ["-std=c++17", "-frounding-math", "-ffp-contract=off", "-shared", "-fPIC",
                                "-o", so] + srcs)
-    return C.CDLL(so)
+    return _PtrSafe(C.CDLL(so))
+
+
+class _PtrSafe:
+    """ctypes passes a bare Python int as a C int; buffer addresses (`arr.ctypes.data`) must go as pointers."""
+
+    def __init__(self, lib):
+        self._lib = lib
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+
+        def call(*args):
+            return fn(*[C.c_void_p(a) if isinstance(a, int) and not isinstance(a, bool) and a >= (1 << 31) else a
+                        for a in args])
+        return call
 
 
 @pytest.mark.parametrize("field", [0, 1])

@@ -23,11 +23,14 @@ def test_noalloc_merkle_root_matches_allocating_entry_point():
     import torch
     import sponge_b200 as S
     from sponge_b200 import _lib as L
+    from oracle import poseidon_ref as R
+    from oracle.c_oracle import COracle
 
     lib = L.lib
     ark, mds = S.find_poseidon_ark_and_mds("bn254", 254, 2, 8, 57, 0)
     cfg = S.PoseidonConfig.new(8, 57, 5, mds, ark, 2, 1, "bn254")
     ctx = cfg.context(0)
+    orc = COracle(R.bn254_config(2, 8, 57), 0)   # the CPU oracle: the check does not rest on psd_merkle_root alone
     try:
         dev = torch.device("cuda:0")
         stream = torch.cuda.current_stream(dev).cuda_stream
@@ -44,6 +47,11 @@ def test_noalloc_merkle_root_matches_allocating_entry_point():
             # new entry point: same inputs, caller-owned output, no allocation inside
             L.check(lib.psd_merkle_root_noalloc(ctx.handle, leaves.data_ptr(), n_leaves, got.data_ptr(), repr_, stream))
             ctx.synchronize(stream)
+            # the same leaves on the host (the synthetic generator is identical on both sides) through the oracle
+            exp = orc.merkle_root(orc.synth(n_leaves, seed))
+            if repr_ == L.REPR_CANONICAL:
+                exp = orc.from_mont(exp.copy())
+            assert np.array_equal(got.cpu().numpy().view(np.uint64).reshape(4), exp)
             return want.cpu().numpy().view(np.uint64), got.cpu().numpy().view(np.uint64)
 
         # call 1: the largest tree the fixed scratch array can hold, Montgomery leaves
