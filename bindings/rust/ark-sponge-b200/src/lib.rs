@@ -14,9 +14,10 @@ pub mod batch;
 use ark_ff::{BigInteger, Fp, FpConfig, PrimeField};
 use ark_sponge::poseidon::{PoseidonConfig, PoseidonSpongeState};
 use ark_sponge::{Absorb, CryptographicSponge, DuplexSpongeMode, FieldBasedCryptographicSponge, FieldElementSize, SpongeExt};
+use std::collections::HashMap;
 use std::ffi::CStr;
 use std::os::raw::c_int;
-use std::sync::Arc;
+use std::sync::{Arc, Mutex, OnceLock, Weak};
 
 /// Turns a status code back into the panic the reference would have raised (shape asserts
 /// poseidon/mod.rs:196-203, unwraps absorb.rs:163); the drop-in must not change error behaviour.
@@ -52,7 +53,50 @@ impl Drop for Ctx {
         unsafe { ffi::psd_ctx_destroy(self.raw) }
     }
 }
+/// Key of the process-wide context cache: device, field and every number of the parameter set.
+#[derive(PartialEq, Eq, Hash, Clone)]
+struct CtxKey {
+    device: i32,
+    field: i32,
+    shape: [u64; 5],   // full_rounds, partial_rounds, alpha, rate, capacity
+    limbs: Vec<u64>,   // ark then mds, Montgomery limb images
+}
+
+fn ctx_cache() -> &'static Mutex<HashMap<CtxKey, Weak<Ctx>>> {
+    static CACHE: OnceLock<Mutex<HashMap<CtxKey, Weak<Ctx>>>> = OnceLock::new();
+    CACHE.get_or_init(|| Mutex::new(HashMap::new()))
+}
+
 impl Ctx {
+    /// The context of this parameter set on `device`: the live one if any sponge or caller still holds
+    /// it, else a new one.  The reference calls `PoseidonSponge::new(&params)` freely and keeps many
+    /// sponges alive at once (poseidon/mod.rs:219-230 clones the parameters into each); here all of them
+    /// share one psd_ctx (streams, staging buffers, constants on the GPU) instead of creating one each.
+    pub fn cached<P: FpConfig<4>>(p: &PoseidonConfig<Fp<P, 4>>, device: i32) -> Arc<Self> {
+        let ark: Vec<Fp<P, 4>> = p.ark.iter().flatten().copied().collect();
+        let mds: Vec<Fp<P, 4>> = p.mds.iter().flatten().copied().collect();
+        let mut limbs: Vec<u64> = Vec::with_capacity(4 * (ark.len() + mds.len()));
+        for e in ark.iter().chain(mds.iter()) {
+            limbs.extend_from_slice(&(e.0).0);
+        }
+        let key = CtxKey {
+            device,
+            field: field_id::<Fp<P, 4>>(),
+            shape: [p.full_rounds as u64, p.partial_rounds as u64, p.alpha, p.rate as u64, p.capacity as u64],
+            limbs,
+        };
+        let mut map = ctx_cache().lock().unwrap();
+        if let Some(live) = map.get(&key).and_then(Weak::upgrade) {
+            return live;
+        }
+        map.retain(|_, w| w.strong_count() > 0);
+        let fresh = Self::new(p, device);
+        map.insert(key, Arc::downgrade(&fresh));
+        fresh
+    }
+
+    /// Always creates a new psd_ctx (identical parameter sets still share one copy of the constants on
+    /// the GPU inside the library).
     pub fn new<P: FpConfig<4>>(p: &PoseidonConfig<Fp<P, 4>>, device: i32) -> Arc<Self> {
         // [round][lane] and [row][col], flattened; the Vec<Fp> memory is the Montgomery limb image
         let ark: Vec<Fp<P, 4>> = p.ark.iter().flatten().copied().collect();
@@ -112,7 +156,7 @@ impl<P: FpConfig<4>> CryptographicSponge for B200PoseidonSponge<P> {
 
     /// poseidon/mod.rs:219-230
     fn new(parameters: &Self::Config) -> Self {
-        Self::with_context(parameters, Ctx::new(parameters, 0))
+        Self::with_context(parameters, Ctx::cached(parameters, 0))
     }
 
     /// poseidon/mod.rs:232-254; the marshalling of `input` is the reference's own (absorb.rs)

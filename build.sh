@@ -27,6 +27,11 @@ for f in 0 1; do
     if newer $o $SRC/tu_sponge.cu $HDRS; then
       run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_TU_T=$t -c -o $o $SRC/tu_sponge.cu
     fi
+    # the same unit with constants staged through shared memory (no constant-bank limit)
+    o=$OBJ/tu_${f}_${t}_smem.o
+    if newer $o $SRC/tu_sponge.cu $HDRS; then
+      run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_TU_T=$t -DPSD_POOL_SHARED=1 -c -o $o $SRC/tu_sponge.cu
+    fi
   done
 done
 # variant-5 unit: BN254 only (for BLS12-381 it measured slower than variant 3: 140 M vs 168 M perm/s on c5;
@@ -34,6 +39,8 @@ done
 for f in 0; do
   o=$OBJ/tu_fp52_${f}.o
   if newer $o $SRC/tu_fp52.cu $HDRS; then run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -c -o $o $SRC/tu_fp52.cu; fi
+  o=$OBJ/tu_fp52_${f}_smem.o
+  if newer $o $SRC/tu_fp52.cu $HDRS; then run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_POOL_SHARED=1 -c -o $o $SRC/tu_fp52.cu; fi
 done
 for u in misc_kernels api; do
   o=$OBJ/$u.o
@@ -46,8 +53,8 @@ done
 fail=0
 for p in "${pids[@]:-}"; do [[ -n "$p" ]] && { wait "$p" || fail=1; }; done
 [[ $fail -eq 0 ]] || { echo "build failed" >&2; exit 1; }
-OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52_0.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o"
-for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o"; done; done
+OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o"
+for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o $OBJ/tu_${f}_${t}_smem.o"; done; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $LIB/libposeidon_b200.so $OBJS -Xcompiler -fPIC
 # CPU oracle (test infrastructure)
 if newer oracle/liboracle.so oracle/poseidon_oracle.c; then

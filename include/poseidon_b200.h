@@ -48,7 +48,7 @@ typedef enum psd_status {
     PSD_ERR_NONCANONICAL = 3, /* a canonical input is >= p (ark-ff from_bigint -> None) */
     PSD_ERR_CUDA = 4,         /* CUDA runtime error; see psd_last_error_string */
     PSD_ERR_UNSUPPORTED = 5,  /* e.g. state width outside [2,9], rate < 2 for Merkle */
-    PSD_ERR_NOMEM = 6         /* host/device allocation failed, or constant bank full */
+    PSD_ERR_NOMEM = 6         /* host/device allocation failed */
 } psd_status;
 
 typedef enum psd_field { PSD_FIELD_BN254_FR = 0, PSD_FIELD_BLS12_381_FR = 1 } psd_field;
@@ -254,15 +254,33 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 0 = dense (ark -> S-box -> dense MDS every round, the reference's operation order),
  * 1 = optimised, fully unrolled rounds,
  * 2 = optimised, compact rolled phases,
- * 3 = 2 + products by round constants through digit tables.  The tables take about 33 KB of the
- *     62 KB constant pool that the contexts of one (field, width) share, so only the first live t=3
- *     context of each field gets them; every other context silently runs variant 2.  (4 is an alias.)
- * 5 = integer S-box + the whole linear layer on the FP64 pipe in 52-bit limbs (BN254 Fr, t <= 3,
- *     alpha 5 or 17).  Its tables (about 54 KB) live in a separate constant pool that one parameter
- *     set nearly fills: the first live eligible context gets it, every other one runs as variant 3.
- * psd_ctx_active_variant reports what a launch on this context really runs (0..5; 4 = the t=5 form of 3). */
+ * 3 = 2 + products by round constants through digit tables (t = 3; 4 = the t = 5 form: lane updates only),
+ * 5 = integer S-box + the whole linear layer on the FP64 pipe in 52-bit limbs (BN254 Fr, t = 2, 3, 5,
+ *     alpha 5 or 17) -- the default where it exists.
+ * A request is served by the best kernel <= it that exists for the context's field, width and home of
+ * constants; psd_ctx_active_variant / psd_ctx_describe report what a launch really runs.
+ *
+ * Where the constants live.  The kernels read round constants either from the 64 KiB constant bank
+ * (one pool per (field, width) plus one for variant 5; fastest) or, in their shared-memory form, from a
+ * copy that every thread block makes of the context's image in global memory.  psd_ctx_create looks for
+ * an identical live parameter set on the device first (such contexts share one image), then for room in
+ * the bank, then falls back to the shared-memory form, which any number of parameter sets can use at
+ * once -- so creating a context never fails for lack of constant-bank space and a second parameter set
+ * of the same shape runs the same algorithm as the first (measured within a few percent; the t = 5
+ * variant-5 tables, 100 KiB, exist in the shared-memory form only). */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
 psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant);
+typedef enum psd_constants_home { PSD_CONSTANTS_BANK = 0, PSD_CONSTANTS_SHARED = 1 } psd_constants_home;
+typedef struct psd_ctx_info {
+    int32_t variant;           /* what psd_ctx_active_variant reports */
+    int32_t constants_home;    /* psd_constants_home of the image that kernel reads */
+    uint32_t image_bytes;      /* size of that image */
+    uint32_t image_shared_by;  /* live contexts on this device using the same image (>= 1) */
+    char kernel_name[96];      /* e.g. "sponge_kernel<bn254,t=3,alpha=5,variant=5>" */
+} psd_ctx_info;
+/* No counterpart in the reference (PoseidonConfig is plain data there); lets a service see which kernel
+ * and which home of constants each of its parameter sets got. */
+psd_status psd_ctx_describe(const psd_ctx* ctx, psd_ctx_info* out);
 
 #ifdef __cplusplus
 }

@@ -36,6 +36,20 @@ class PsdParams(C.Structure):
     ]
 
 
+class PsdCtxInfo(C.Structure):
+    """struct psd_ctx_info (psd_ctx_describe)."""
+    _fields_ = [
+        ("variant", C.c_int32),
+        ("constants_home", C.c_int32),
+        ("image_bytes", C.c_uint32),
+        ("image_shared_by", C.c_uint32),
+        ("kernel_name", C.c_char * 96),
+    ]
+
+
+CONSTANTS_BANK, CONSTANTS_SHARED = 0, 1
+
+
 class PoseidonB200Error(RuntimeError):
     def __init__(self, status: int, message: str):
         super().__init__(f"{status_name(status)}: {message}")
@@ -105,6 +119,7 @@ _PROTOS = {
     "psd_imad_peak": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "psd_ctx_set_variant": (_i, [_vp, _i]),
     "psd_ctx_active_variant": (_i, [_vp, C.POINTER(C.c_int)]),
+    "psd_ctx_describe": (_i, [_vp, C.POINTER(PsdCtxInfo)]),
 }
 
 for _name, (_res, _args) in _PROTOS.items():

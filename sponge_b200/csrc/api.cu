@@ -70,13 +70,23 @@ static std::vector<SpongeKernelEntry>& sponge_kernels() {
 void register_pool_uploader(int field, int t, PoolUploadFn fn) { pool_uploaders().push_back(PoolUploader{field, t, fn}); }
 void register_sponge_kernel(const SpongeKernelEntry& e) { sponge_kernels().push_back(e); }
 
-static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, int variant) {
+// Best registered kernel for (field, t, alpha) of pool kind `pool` whose variant is <= `variant` and
+// whose table requirements the descriptor meets (variant 3 reads the full digit tables, 4 the lane-update
+// ones, 1-2 the regrouped constants, 5 the 52-bit-limb tables).
+static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, int variant, int pool,
+                                            const PermDesc* d = nullptr) {
     const SpongeKernelEntry* best = nullptr;
     int best_score = -1;
     for (const auto& e : sponge_kernels()) {
-        if (e.field != field || e.t != t) continue;
+        if (e.field != field || e.t != t || e.pool != pool) continue;
         if (e.alpha != 0 && e.alpha != alpha) continue;
         if (e.variant > variant) continue;
+        if (d) {
+            if (e.variant == 5 && !d->fp_ok) continue;
+            if (e.variant == 3 && d->ctab_ok != 1) continue;
+            if (e.variant == 4 && d->ctab_ok != 2) continue;
+            if ((e.variant == 1 || e.variant == 2) && !d->opt_ok) continue;
+        }
         const int score = (e.alpha == alpha ? 2 : 0) + e.variant * 4;
         if (score > best_score) {
             best_score = score;
@@ -85,30 +95,45 @@ static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, in
     }
     return best;
 }
+static int kernel_index(const SpongeKernelEntry* k) { return (int)(k - sponge_kernels().data()); }
 
 static std::atomic<uint64_t> g_launches{0};
 
 // ------------------------------------------------------------------------------------------------
-// Constant-bank slots: one 62 KiB pool per (device, field, t) -- the kernel unit's own c_pool --
-// shared by the live contexts of that kind.  The small-kernel unit keeps [R, R^2] of both fields at
-// fixed offsets (kMiscOne/kMiscR2), uploaded once per device.
+// Where a context's constants live on its device.  Two homes:
+//   bank   a slot of the 62 KiB constant-bank pool of the kernel unit for (field, t) -- or of the
+//          variant-5 unit, key kFp52PoolKey -- read by the kernels through uniform loads;
+//   smem   a buffer in global memory that the shared-memory form of the kernels copies into each block's
+//          shared memory; no size limit worth mentioning and no competition between parameter sets.
+// Contexts whose images are byte-identical share one placement (reference pattern: many
+// PoseidonSponge::new(&params) with the same params, mod.rs:219-230), so the bank only ever holds
+// distinct parameter sets; when it is full the next set goes to the smem home instead of being refused.
+// The small-kernel unit keeps [R, R^2] of both fields at fixed offsets, uploaded once per device.
 // ------------------------------------------------------------------------------------------------
+enum : int { kPoolBank = 0, kPoolSmem = 1 };
+
+struct Placement {
+    int device = 0, field = 0, key = 0;
+    int kind = kPoolBank;
+    uint32_t off = 0;              // bank: word offset of the slot
+    uint32_t* d_img = nullptr;     // smem: the image in global memory
+    std::vector<uint32_t> words;   // the image (kept for the identity check)
+    int refs = 0;
+};
 struct PoolSlot {
     uint32_t off, len;
 };
 struct DevicePool {
     std::mutex mu;
-    std::vector<PoolSlot> used;   // sorted by off
+    std::vector<PoolSlot> used;    // sorted by off
+    std::vector<Placement*> live;
 };
 static DevicePool g_pools[64][2][kFp52PoolKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool
 static std::once_flag g_misc_once[64];
 static inline uint32_t misc_one_off(int field) { return (uint32_t)field * 16; }
 static inline uint32_t misc_r2_off(int field) { return (uint32_t)field * 16 + 8; }
 
-static bool pool_alloc(int device, int field, int t, uint32_t len, uint32_t* off, bool* was_empty) {
-    DevicePool& p = g_pools[device][field][t];
-    std::lock_guard<std::mutex> lk(p.mu);
-    if (was_empty) *was_empty = p.used.empty();
+static bool slot_alloc(DevicePool& p, uint32_t len, uint32_t* off) {
     uint32_t cur = 0;
     size_t pos = 0;
     for (; pos < p.used.size(); pos++) {
@@ -120,20 +145,78 @@ static bool pool_alloc(int device, int field, int t, uint32_t len, uint32_t* off
     *off = cur;
     return true;
 }
-static bool pool_is_empty(int device, int field, int t) {
-    DevicePool& p = g_pools[device][field][t];
-    std::lock_guard<std::mutex> lk(p.mu);
-    return p.used.empty();
-}
-static void pool_free(int device, int field, int t, uint32_t off) {
-    DevicePool& p = g_pools[device][field][t];
-    std::lock_guard<std::mutex> lk(p.mu);
+static void slot_free(DevicePool& p, uint32_t off) {
     for (size_t i = 0; i < p.used.size(); i++) {
         if (p.used[i].off == off) {
             p.used.erase(p.used.begin() + i);
             return;
         }
     }
+}
+
+// Finds or creates the placement of `words` (a multiple of 8 words) on `device`, which must be current.
+// Tries, in order: an identical live image, a bank slot (if try_bank), a global-memory buffer (if
+// try_smem).  The upload is complete when this returns.  nullptr: neither home was possible; *cerr holds
+// the CUDA error if one occurred.
+static Placement* placement_acquire(int device, int field, int key, const std::vector<uint32_t>& words, bool try_bank,
+                                    bool try_smem, cudaError_t* cerr) {
+    *cerr = cudaSuccess;
+    DevicePool& p = g_pools[device][field][key];
+    std::lock_guard<std::mutex> lk(p.mu);
+    for (Placement* q : p.live) {
+        if (q->words == words && ((q->kind == kPoolBank && try_bank) || (q->kind == kPoolSmem && try_smem))) {
+            q->refs++;
+            return q;
+        }
+    }
+    uint32_t off = 0;
+    PoolUploadFn up = try_bank ? find_uploader(field, key) : nullptr;
+    if (up && words.size() <= kConstPoolWords && slot_alloc(p, (uint32_t)words.size(), &off)) {
+        cudaError_t e = (cudaError_t)up(off, words.data(), (uint32_t)words.size(), nullptr);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(nullptr);
+        if (e != cudaSuccess) {
+            slot_free(p, off);
+            *cerr = e;
+            return nullptr;
+        }
+        Placement* q = new Placement();
+        q->device = device, q->field = field, q->key = key, q->kind = kPoolBank, q->off = off, q->words = words, q->refs = 1;
+        p.live.push_back(q);
+        return q;
+    }
+    if (try_smem && words.size() <= kSmemPoolMaxWords) {
+        uint32_t* d = nullptr;
+        cudaError_t e = cudaMalloc(&d, words.size() * 4);
+        if (e == cudaSuccess) e = cudaMemcpy(d, words.data(), words.size() * 4, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            if (d) cudaFree(d);
+            cudaGetLastError();
+            *cerr = e;
+            return nullptr;
+        }
+        Placement* q = new Placement();
+        q->device = device, q->field = field, q->key = key, q->kind = kPoolSmem, q->d_img = d, q->words = words, q->refs = 1;
+        p.live.push_back(q);
+        return q;
+    }
+    return nullptr;
+}
+
+// Drops one reference; the last one frees the slot / buffer (device must be current for the smem home).
+static void placement_release(Placement* q) {
+    if (!q) return;
+    DevicePool& p = g_pools[q->device][q->field][q->key];
+    std::lock_guard<std::mutex> lk(p.mu);
+    if (--q->refs > 0) return;
+    for (size_t i = 0; i < p.live.size(); i++) {
+        if (p.live[i] == q) {
+            p.live.erase(p.live.begin() + i);
+            break;
+        }
+    }
+    if (q->kind == kPoolBank) slot_free(p, q->off);
+    else if (q->d_img) cudaFree(q->d_img);
+    delete q;
 }
 
 }  // namespace psd
@@ -153,15 +236,13 @@ struct psd_ctx {
     uint32_t full_rounds = 0, partial_rounds = 0, rate = 0, capacity = 0, t = 0;
     uint64_t alpha = 0;
     std::vector<Fe> ark_mont, mds_mont;   // Montgomery copies of the parameters
-    PermDesc desc{};       // offsets into the sponge-kernel unit's pool
+    PermDesc desc{};       // offsets into the home of the integer kernels' image (pl_int)
     PermDesc misc_desc{};  // same parameters with one/r2 offsets of the small-kernel unit's pool
-    uint32_t pool_off = 0, pool_len = 0;
-    bool pool_held = false;
-    // variant 5 (tu_fp52.cu) has its own pool and descriptor; fdesc.fp_ok == 0 when the context has none
+    Placement* pl_int = nullptr;
+    // variant 5 (tu_fp52.cu) has its own image and descriptor; fdesc.fp_ok == 0 when the context has none
     PermDesc fdesc{};
-    uint32_t fpool_off = 0, fpool_len = 0;
-    bool fpool_held = false;
-    int variant = 5;   // degrades to 3 / 2 / 0 by what the context has constants for (resolve_variant)
+    Placement* pl_fp = nullptr;
+    int variant = 5;   // degrades to 3 / 2 / 0 by what the context has constants for (resolve_kernel)
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;
@@ -169,8 +250,9 @@ struct psd_ctx {
     void* stage_in[kStageSlots] = {nullptr, nullptr, nullptr};
     void* stage_out[kStageSlots] = {nullptr, nullptr, nullptr};
     size_t stage_in_bytes = 0, stage_out_bytes = 0;
-    int32_t* d_err = nullptr;
+    int32_t* d_err = nullptr;   // non-canonical-input flag of the one-shot calls (batches have their own)
     int32_t* h_err = nullptr;   // pinned
+    std::mutex err_mu;          // serialises readers of the flag pair above
     // psd_merkle_root work space, kept between calls (cudaMalloc/cudaFree of hundreds of MB per call
     // cost 5-25 ms and made the step time jitter); grown on demand, released with the context
     std::mutex merkle_mu;
@@ -246,16 +328,22 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
     // than a persistent grid-stride grid (blocks start staggered, so warps sit in different phases of
     // the permutation and the multiplier pipe stays fed), and the kernel has no per-thread loop so
     // that ptxas keeps round constants on the uniform datapath.
-    (void)ctx;
     LaunchCfg cfg;
     cfg.block = 128;
-    if (k->variant == 5) {
+    const uint64_t sms = (uint64_t)std::max(1, ctx->sm_count);
+    if (k->pool == kPoolSmem) {
+        // Shared-memory form: every block copies the constant image first, so blocks are as large as the
+        // kernel's launch bounds allow once the batch fills the SMs, and shrink (in warps) for small batches
+        // so that every SM still gets one.
+        const uint64_t max_block = k->variant == 5 ? 512 : 448;
+        const uint64_t per_sm = (n + sms - 1) / sms;
+        cfg.block = (int)std::min<uint64_t>(max_block, std::max<uint64_t>(32, (per_sm + 31) / 32 * 32));
+    } else if (k->variant == 5) {
         // Variant 5's partial-round body (1.5 K instructions) does not fit the instruction caches when
         // the warps of a scheduler sit at different places in it.  Warps of ONE block start together and
         // stay close, so large blocks share their instruction fetches: measured on B200 (c2) 162.8 M
         // perm/s with 128-thread blocks, 172.9 M with 256, 175.0 M with 512 (one 128-register block per
         // SM).  Small batches keep smaller blocks so that every SM still gets one.
-        const uint64_t sms = (uint64_t)std::max(1, ctx->sm_count);
         cfg.block = n >= 512 * sms ? 512 : n >= 256 * sms ? 256 : 128;
         const int forced = env_int("PSD_FP52_BLOCK", 0);   // tuning runs
         if (forced >= 32 && forced <= 512 && forced % 32 == 0) cfg.block = forced;
@@ -273,30 +361,55 @@ LaunchCfg misc_cfg(const psd_ctx* ctx, uint64_t n) {
     return cfg;
 }
 
-// the kernel variant a launch really uses: the requested one, degraded to what this context has
-// constants for
-int resolve_variant(const psd_ctx* ctx) {
-    if (ctx->variant >= 5 && ctx->fdesc.fp_ok) return 5;
-    int variant = (ctx->variant >= 1 && ctx->desc.opt_ok) ? ctx->variant : 0;
-    if (variant >= 3) variant = ctx->desc.ctab_ok == 1 ? 3 : ctx->desc.ctab_ok == 2 ? 4 : 2;
-    return variant;
+// What a launch on this context runs: the requested variant, degraded to what the context has constants
+// and kernels for, together with the image (placement + descriptor) that kernel reads.
+struct Resolved {
+    const SpongeKernelEntry* k = nullptr;
+    const Placement* pl = nullptr;
+    const PermDesc* d = nullptr;
+};
+Resolved resolve_kernel(const psd_ctx* ctx) {
+    Resolved r;
+    if (ctx->variant >= 5 && ctx->pl_fp && ctx->fdesc.fp_ok) {
+        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 5, ctx->pl_fp->kind, &ctx->fdesc);
+        if (k && k->variant == 5) {
+            r.k = k, r.pl = ctx->pl_fp, r.d = &ctx->fdesc;
+            return r;
+        }
+    }
+    if (!ctx->pl_int) return r;
+    const int want = std::min(ctx->variant, 4);
+    r.k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, want, ctx->pl_int->kind, &ctx->desc);
+    r.pl = ctx->pl_int, r.d = &ctx->desc;
+    return r;
 }
 
+// Kernels of the shared-memory form need the opt-in shared-memory size; set once per (kernel, device).
+std::atomic<uint64_t> g_smem_attr_done[512];
+
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
-    const int variant = resolve_variant(ctx);
-    const bool fp52 = variant == 5;
-    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, variant);
+    const Resolved r = resolve_kernel(ctx);
+    const SpongeKernelEntry* k = r.k;
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
-    if (a.n > (uint64_t)0x7fffffff * 128) return fail(PSD_ERR_ARG, "batch too large for one launch (%llu sponges)", (unsigned long long)a.n);
+    if (a.n > (uint64_t)0x7fffffff * 32) return fail(PSD_ERR_ARG, "batch too large for one launch (%llu sponges)", (unsigned long long)a.n);
     LaunchCfg cfg = sponge_cfg(ctx, k, a.n);
-    if (fp52) {
-        SpongeArgs b = a;
-        b.d = ctx->fdesc;   // same parameters, offsets into the variant-5 unit's pool
-        k->fn<<<cfg.grid, cfg.block, 0, stream>>>(b);
-    } else {
-        k->fn<<<cfg.grid, cfg.block, 0, stream>>>(a);
+    SpongeArgs b = a;
+    b.d = *r.d;   // same parameters, offsets into the home of this kernel's image
+    size_t smem = 0;
+    if (k->pool == kPoolSmem) {
+        b.pool_img = r.pl->d_img;
+        b.pool_words = (uint32_t)r.pl->words.size();
+        smem = (size_t)b.pool_words * 4;
+        const int ki = kernel_index(k);
+        const uint64_t bit = 1ull << ctx->device;
+        if (ki >= 0 && ki < 512 && !(g_smem_attr_done[ki].load(std::memory_order_acquire) & bit)) {
+            PSD_CUDA(cudaFuncSetAttribute((const void*)k->fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(kSmemPoolMaxWords * 4)));
+            g_smem_attr_done[ki].fetch_or(bit, std::memory_order_release);
+        }
     }
+    k->fn<<<cfg.grid, cfg.block, smem, stream>>>(b);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     PSD_CUDA(cudaGetLastError());
     return PSD_OK;
@@ -313,15 +426,19 @@ SpongeArgs base_args(const psd_ctx* ctx, uint64_t n) {
 }
 
 // Reads and clears the non-canonical-input flag once `stream` is idle.
-psd_status check_err_flag(psd_ctx* ctx, cudaStream_t stream) {
-    PSD_CUDA(cudaMemcpyAsync(ctx->h_err, ctx->d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+psd_status read_err_flag(int32_t* h_err, int32_t* d_err, cudaStream_t stream) {
+    PSD_CUDA(cudaMemcpyAsync(h_err, d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
     PSD_CUDA(cudaStreamSynchronize(stream));
-    if (*ctx->h_err) {
-        PSD_CUDA(cudaMemsetAsync(ctx->d_err, 0, sizeof(int32_t), stream));
+    if (*h_err) {
+        PSD_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int32_t), stream));
         PSD_CUDA(cudaStreamSynchronize(stream));
         return fail(PSD_ERR_NONCANONICAL, "a canonical input element was >= p");
     }
     return PSD_OK;
+}
+psd_status check_err_flag(psd_ctx* ctx, cudaStream_t stream) {
+    std::lock_guard<std::mutex> lk(ctx->err_mu);
+    return read_err_flag(ctx->h_err, ctx->d_err, stream);
 }
 
 psd_status ensure_staging(psd_ctx* ctx, size_t in_bytes, size_t out_bytes) {
@@ -380,12 +497,17 @@ struct StagedCall {
     uint32_t out_bytes_per; // bytes per sponge copied out (squeeze_bytes)
     int layout;
     bool in_place;          // output overwrites the input staging buffer (permute_batch)
+    // Only sponges [first0, first0 + count) of the n in the host buffers are processed (a shard of a
+    // multi-device call); count == 0 means all of them.
+    uint64_t first0 = 0, count = 0;
 };
 
 // H2D -> kernel -> D2H over kStageSlots streams; `fill` completes the SpongeArgs for a chunk.
 template <class Fill>
 psd_status run_staged(psd_ctx* ctx, const StagedCall& c, Fill fill) {
     if (c.n == 0) return PSD_OK;
+    const uint64_t begin = c.first0, end = c.count ? c.first0 + c.count : c.n;
+    if (begin >= end) return PSD_OK;
     std::lock_guard<std::mutex> lk(ctx->stage_mu);
     const size_t in_per = (size_t)c.in_w * 32;
     const size_t out_per = c.out_bytes_per ? c.out_bytes_per : (size_t)c.out_w * 32;
@@ -396,14 +518,18 @@ psd_status run_staged(psd_ctx* ctx, const StagedCall& c, Fill fill) {
     // to end at 2^16, 174.4 M at 2^17, 173.6 M at 2^18, against 175.1 M device-resident).
     const size_t per = std::max<size_t>(1, in_per + (c.in_place ? 0 : out_per));
     static const int chunk_log2 = env_int("PSD_STAGE_CHUNK_LOG2", 17);   // development knob
-    uint64_t chunk = std::max<uint64_t>((256ull << 20) / per, 1ull << 16);
+    // Bounded by bytes first (256 MiB per slot); the 2^16-sponge floor that keeps launches large applies only
+    // while a slot stays under 512 MiB, so wide inputs (c5: 32 KiB per sponge) get smaller chunks instead of
+    // multi-GiB staging buffers.
+    uint64_t chunk = std::max<uint64_t>((256ull << 20) / per, std::min<uint64_t>(1ull << 16, (512ull << 20) / per));
+    chunk = std::max<uint64_t>(chunk, 1);
     chunk = std::min<uint64_t>(chunk, 1ull << chunk_log2);
-    chunk = std::min<uint64_t>(chunk, c.n);
+    chunk = std::min<uint64_t>(chunk, end - begin);
     psd_status st = ensure_staging(ctx, std::max<size_t>(chunk * in_per, 16), c.in_place ? 0 : std::max<size_t>(chunk * out_per, 16));
     if (st != PSD_OK) return st;
     int slot = 0;
-    for (uint64_t first = 0; first < c.n; first += chunk, slot = (slot + 1) % kStageSlots) {
-        const uint64_t cnt = std::min<uint64_t>(chunk, c.n - first);
+    for (uint64_t first = begin; first < end; first += chunk, slot = (slot + 1) % kStageSlots) {
+        const uint64_t cnt = std::min<uint64_t>(chunk, end - first);
         cudaStream_t s = ctx->streams[slot];
         void* d_in = ctx->stage_in[slot];
         void* d_out = c.in_place ? d_in : ctx->stage_out[slot];
@@ -430,6 +556,65 @@ psd_status check_batch_args(const psd_ctx* ctx, const void* p, int layout, int r
     if (!p) return fail(PSD_ERR_ARG, "null buffer");
     if (!valid_enum(layout, 1) || !valid_enum(repr, 1) || !valid_enum(mem, 1))
         return fail(PSD_ERR_ARG, "bad layout/repr/mem value");
+    return PSD_OK;
+}
+
+bool grow_device_buffer(void** buf, size_t* have, size_t need) {
+    if (need <= *have) return true;
+    if (*buf) cudaFree(*buf);
+    *buf = nullptr;
+    *have = 0;
+    if (cudaMalloc(buf, need) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    *have = need;
+    return true;
+}
+
+// Host leaves -> the context's device copy (kept between calls).  Caller holds merkle_mu.
+psd_status merkle_upload_leaves(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, cudaStream_t s, const uint32_t** d_out) {
+    if (!grow_device_buffer(&ctx->merkle_leaves, &ctx->merkle_leaves_bytes, n_leaves * 32))
+        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for leaves failed", n_leaves * 32);
+    if (cudaMemcpyAsync(ctx->merkle_leaves, leaves, n_leaves * 32, cudaMemcpyHostToDevice, s) != cudaSuccess)
+        return fail(PSD_ERR_CUDA, "leaf upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    *d_out = static_cast<const uint32_t*>(ctx->merkle_leaves);
+    return PSD_OK;
+}
+
+// Queues, on stream s, the reduction of n_leaves (a power of two >= 2) device leaves in src_repr to ONE
+// element in dst_repr: every level is one launch of the sponge kernel over the pairs of the level below
+// (absorb 2, squeeze 1), intermediate levels in Montgomery form in the context's scratch buffer
+// ([level 1: n/2][level 2: n/4] elements, ping-pong above that; grown here, kept between calls).  The
+// root goes to `dst` if given (device pointer), else into the scratch buffer; *where tells which.
+// Caller holds ctx->merkle_mu and the device is current.  Nothing is synchronised here.
+psd_status merkle_reduce_async(psd_ctx* ctx, const uint32_t* src, int src_repr, size_t n_leaves, uint32_t* dst,
+                               int dst_repr, cudaStream_t s, const uint32_t** where) {
+    const size_t half = n_leaves / 2, quarter = std::max<size_t>(n_leaves / 4, 1);
+    if (!grow_device_buffer(&ctx->merkle_scratch, &ctx->merkle_scratch_bytes, (half + quarter) * 32))
+        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for Merkle levels failed", (half + quarter) * 32);
+    uint32_t* scratch = static_cast<uint32_t*>(ctx->merkle_scratch);
+    uint32_t* bufs[2] = {scratch, scratch + half * 8};
+    int which = 0;
+    for (size_t pairs = half; pairs >= 1; pairs /= 2) {
+        SpongeArgs a = base_args(ctx, pairs);
+        a.in = src;
+        a.n_absorb = 2;
+        a.in_layout = kLayoutAos;
+        a.in_repr = src_repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = 1;
+        a.out = (pairs == 1 && dst) ? dst : bufs[which];
+        a.out_layout = kLayoutAos;
+        a.out_repr = pairs == 1 ? dst_repr : kReprMontgomery;
+        psd_status st = launch(ctx, a, s);
+        if (st != PSD_OK) return st;
+        src = a.out;
+        src_repr = kReprMontgomery;
+        which ^= 1;
+        if (pairs == 1) break;
+    }
+    if (where) *where = src;
     return PSD_OK;
 }
 
@@ -580,67 +765,94 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     if (t <= 5)
         append_optimised_constants(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, ctx->desc, img);
 
-    // Digit tables for constant products (variant 3) are large (about 8x the constants they cover), so a
-    // context gets them only where a kernel uses them (t = 3: +7.5 % on C2, +3.9 % on C5) and only if it
-    // is the first live context of its (field, t) -- later ones run variant 2 and keep the bank free.
+    // Digit tables for constant products (variant 3; t = 5: lane-update tables only, variant 4) are about 8x
+    // the constants they cover.  The image WITH tables is tried first: an identical live image, a bank slot,
+    // or -- when the bank is taken by other parameter sets -- the shared-memory home, whose kernels have
+    // the same tables (PSD_PREFER_BANK=1 reverses the last two for measurements: bank without tables first).
     const size_t base_words = img.size();
     const PermDesc base_desc = ctx->desc;
-    if (ctx->desc.opt_ok && pool_is_empty(device, p->field, (int)t)) {
+    if (ctx->desc.opt_ok) {
         if (t == 3)
             append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img);
-        else if (t == 5 && p->alpha == 5)   // the full set does not fit at t = 5: lane-update tables only
+        else if (t == 5 && p->alpha == 5)   // the full set does not fit the bank at t = 5: lane-update tables only
             append_digit_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->mds_mont, ctx->desc, img, true);
     }
+    while (img.size() % 8) img.push_back(0);
 
     DeviceGuard guard(device);
     if (!guard.ok) {
         delete ctx;
         return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", device);
     }
-    ctx->pool_len = (uint32_t)img.size();
-    if (!pool_alloc(device, p->field, (int)t, ctx->pool_len, &ctx->pool_off, nullptr)) {
-        const bool had_tables = img.size() > base_words;
-        if (had_tables) {   // retry without the digit tables
-            img.resize(base_words);
-            ctx->desc = base_desc;
-            ctx->pool_len = (uint32_t)img.size();
-        }
-        if (!had_tables || !pool_alloc(device, p->field, (int)t, ctx->pool_len, &ctx->pool_off, nullptr)) {
-            delete ctx;
-            return fail(PSD_ERR_NOMEM, "constant bank full: %u words needed; destroy unused contexts of this field and width",
-                        (unsigned)img.size());
-        }
-    }
-    ctx->pool_held = true;
-    offset_desc(ctx->desc, ctx->pool_off);
-
-    // Variant 5 (FP64-pipe linear layer): its own image [ark of round 0][mds][one][r2][52-bit-limb tables] in the
-    // pool of tu_fp52.cu, for the parameter sets that unit has kernels for, when that pool has room
-    // (one parameter set nearly fills it, so in practice the first live context gets it).
-    std::vector<uint32_t> fimg;
     {
-        const SpongeKernelEntry* fk = find_kernel(p->field, (int)t, p->alpha, 5);
-        if (fk && fk->variant == 5 && fk->alpha == p->alpha) {
+        static const bool prefer_bank = env_int("PSD_PREFER_BANK", 0) != 0;
+        static const bool force_smem = env_int("PSD_FORCE_SMEM", 0) != 0;   // test / measurement knob
+        const bool has_tables = ctx->desc.ctab_ok != 0;
+        cudaError_t cerr = cudaSuccess;
+        if (has_tables) {
+            const SpongeKernelEntry* sk = find_kernel(p->field, (int)t, p->alpha, 4, kPoolSmem, &ctx->desc);
+            const bool smem_tables = sk && sk->variant >= 3;
+            ctx->pl_int = placement_acquire(device, p->field, (int)t, img, !force_smem, smem_tables && !prefer_bank, &cerr);
+        }
+        if (!ctx->pl_int && cerr == cudaSuccess) {
+            std::vector<uint32_t> base(img.begin(), img.begin() + base_words);
+            while (base.size() % 8) base.push_back(0);
+            ctx->pl_int = placement_acquire(device, p->field, (int)t, base, !force_smem, true, &cerr);
+            if (ctx->pl_int) {
+                ctx->desc = base_desc;
+                img.swap(base);
+            }
+        }
+        if (!ctx->pl_int) {
+            delete ctx;
+            if (cerr != cudaSuccess) return fail(PSD_ERR_CUDA, "uploading the constants failed: %s", cudaGetErrorString(cerr));
+            return fail(PSD_ERR_NOMEM, "no home for the constant image (%zu words)", img.size());
+        }
+        if (ctx->pl_int->kind == kPoolBank) offset_desc(ctx->desc, ctx->pl_int->off);
+    }
+
+    // Variant 5 (FP64-pipe linear layer): its own image [ark of round 0][mds][one][r2][52-bit-limb tables],
+    // for the parameter sets some unit has variant-5 kernels for.  Home: the pool of tu_fp52.cu when the
+    // image fits and the pool has room (one t = 3 parameter set nearly fills it), else shared memory.
+    {
+        const SpongeKernelEntry* fk_bank = find_kernel(p->field, (int)t, p->alpha, 5, kPoolBank);
+        const SpongeKernelEntry* fk_smem = find_kernel(p->field, (int)t, p->alpha, 5, kPoolSmem);
+        const bool bank_ok = fk_bank && fk_bank->variant == 5 && fk_bank->alpha == p->alpha;
+        const bool smem_ok = fk_smem && fk_smem->variant == 5 && fk_smem->alpha == p->alpha;
+        if (bank_ok || smem_ok) {
+            // base offsets are image-relative in base_desc
+            std::vector<uint32_t> fimg;
             PermDesc fd = base_desc;
             fd.opt_ok = fd.ctab_ok = 0;
             fd.pre_mds_off = fd.sparse_off = fd.post_ark_off = 0;
+            fd.ct_m00_off = fd.ct_mds_off = fd.ct_pre_off = fd.ct_sparse_off = 0;
             // [ark of round 0][mds][one][r2]: the later round constants are inside the tables
-            fimg.assign(img.begin(), img.begin() + t * 8);
+            auto push_fe2 = [&fimg](const Fe& f) {
+                for (int k = 0; k < 4; k++) {
+                    fimg.push_back((uint32_t)f.v[k]);
+                    fimg.push_back((uint32_t)(f.v[k] >> 32));
+                }
+            };
+            fd.ark_off = 0;
+            for (uint32_t j = 0; j < t; j++) push_fe2(ctx->ark_mont[j]);
             fd.mds_off = (uint32_t)fimg.size();
-            fimg.insert(fimg.end(), img.begin() + base_desc.mds_off, img.begin() + base_desc.mds_off + t * t * 8);
+            for (const Fe& f : ctx->mds_mont) push_fe2(f);
             fd.one_off = (uint32_t)fimg.size();
-            fimg.insert(fimg.end(), img.begin() + base_desc.one_off, img.begin() + base_desc.one_off + 8);
+            push_fe2(hf_one(*hf));
             fd.r2_off = (uint32_t)fimg.size();
-            fimg.insert(fimg.end(), img.begin() + base_desc.r2_off, img.begin() + base_desc.r2_off + 8);
+            push_fe2(r2);
             append_fp52_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, fd, fimg);
-            if (fd.fp_ok && fimg.size() <= kConstPoolWords &&
-                pool_alloc(device, p->field, kFp52PoolKey, (uint32_t)fimg.size(), &ctx->fpool_off, nullptr)) {
-                ctx->fpool_len = (uint32_t)fimg.size();
-                ctx->fpool_held = true;
-                offset_desc(fd, ctx->fpool_off);
-                ctx->fdesc = fd;
-            } else {
-                fimg.clear();
+            if (fd.fp_ok) {
+                static const bool force_smem = env_int("PSD_FORCE_SMEM", 0) != 0;
+                cudaError_t cerr = cudaSuccess;
+                ctx->pl_fp = placement_acquire(device, p->field, kFp52PoolKey, fimg, bank_ok && !force_smem, smem_ok, &cerr);
+                if (ctx->pl_fp) {
+                    if (ctx->pl_fp->kind == kPoolBank) offset_desc(fd, ctx->pl_fp->off);
+                    ctx->fdesc = fd;
+                } else if (cerr != cudaSuccess) {
+                    psd_ctx_destroy(ctx);
+                    return fail(PSD_ERR_CUDA, "uploading the variant-5 tables failed: %s", cudaGetErrorString(cerr));
+                }
             }
         }
     }
@@ -664,14 +876,6 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     CTX_CUDA(cudaHostAlloc(&ctx->h_err, sizeof(int32_t), cudaHostAllocDefault));
     *ctx->h_err = 0;
     {
-        PoolUploadFn up = find_uploader(ctx->field, (int)t);
-        if (!up) return cleanup(fail(PSD_ERR_UNSUPPORTED, "no kernels for field %d, t=%u in this build", ctx->field, t));
-        CTX_CUDA(up(ctx->pool_off, img.data(), (uint32_t)img.size(), nullptr));
-        if (ctx->fpool_held) {
-            PoolUploadFn fup = find_uploader(ctx->field, kFp52PoolKey);
-            if (!fup) return cleanup(fail(PSD_ERR_UNSUPPORTED, "variant-5 kernels without a pool uploader"));
-            CTX_CUDA(fup(ctx->fpool_off, fimg.data(), (uint32_t)fimg.size(), nullptr));
-        }
         // [R, R^2] of both fields for the small kernels (convert / synth), once per device
         cudaError_t misc_err = cudaSuccess;
         std::call_once(g_misc_once[device], [&] {
@@ -691,7 +895,7 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->misc_desc.r2_off = misc_r2_off(ctx->field);
     CTX_CUDA(cudaDeviceSynchronize());
 #undef CTX_CUDA
-    if (!find_kernel(ctx->field, (int)t, ctx->alpha, ctx->variant))
+    if (!resolve_kernel(ctx).k)
         return cleanup(fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u in this build", ctx->field, t));
     *out = ctx;
     return PSD_OK;
@@ -724,9 +928,9 @@ static void ctx_teardown(psd_ctx* ctx) {
         if (ctx->h_err) cudaFreeHost(ctx->h_err);
         if (ctx->merkle_scratch) cudaFree(ctx->merkle_scratch);
         if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
+        placement_release(ctx->pl_int);
+        placement_release(ctx->pl_fp);
     }
-    if (ctx->pool_held) pool_free(ctx->device, ctx->field, (int)ctx->t, ctx->pool_off);
-    if (ctx->fpool_held) pool_free(ctx->device, ctx->field, kFp52PoolKey, ctx->fpool_off);
     delete ctx;
 }
 
@@ -753,9 +957,22 @@ psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
 
 psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant) {
     if (!ctx || !variant) return fail(PSD_ERR_ARG, "null argument");
-    const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, resolve_variant(ctx));
+    const SpongeKernelEntry* k = resolve_kernel(ctx).k;
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     *variant = k->variant;
+    return PSD_OK;
+}
+
+psd_status psd_ctx_describe(const psd_ctx* ctx, psd_ctx_info* out) {
+    if (!ctx || !out) return fail(PSD_ERR_ARG, "null argument");
+    const Resolved r = resolve_kernel(ctx);
+    if (!r.k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
+    memset(out, 0, sizeof *out);
+    out->variant = r.k->variant;
+    out->constants_home = r.pl->kind == kPoolBank ? PSD_CONSTANTS_BANK : PSD_CONSTANTS_SHARED;
+    out->image_bytes = (uint32_t)(r.pl->words.size() * 4);
+    out->image_shared_by = (uint32_t)r.pl->refs;
+    snprintf(out->kernel_name, sizeof out->kernel_name, "%s", r.k->name);
     return PSD_OK;
 }
 
@@ -1005,64 +1222,23 @@ psd_status psd_merkle_root(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves
         PSD_CUDA(cudaStreamSynchronize(s));
         return PSD_OK;
     }
-    // scratch: [level 1: n/2][level 2: n/4] elements, ping-pong above that; Montgomery inside
-    const size_t half = n_leaves / 2, quarter = std::max<size_t>(n_leaves / 4, 1);
     std::lock_guard<std::mutex> lk(ctx->merkle_mu);
-    auto grow = [](void** buf, size_t* have, size_t need) -> bool {
-        if (need <= *have) return true;
-        if (*buf) cudaFree(*buf);
-        *buf = nullptr;
-        *have = 0;
-        if (cudaMalloc(buf, need) != cudaSuccess) {
-            cudaGetLastError();
-            return false;
-        }
-        *have = need;
-        return true;
-    };
-    if (!grow(&ctx->merkle_scratch, &ctx->merkle_scratch_bytes, (half + quarter) * 32))
-        return fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for Merkle levels failed", (half + quarter) * 32);
-    uint32_t* scratch = static_cast<uint32_t*>(ctx->merkle_scratch);
     psd_status result = PSD_OK;
     do {
         const uint32_t* src = as_u32(leaves);
         if (mem == PSD_MEM_HOST) {
-            if (!grow(&ctx->merkle_leaves, &ctx->merkle_leaves_bytes, n_leaves * 32)) {
-                result = fail(PSD_ERR_NOMEM, "cudaMalloc(%zu) for leaves failed", n_leaves * 32);
-                break;
-            }
-            uint32_t* d_leaves = static_cast<uint32_t*>(ctx->merkle_leaves);
-            if (cudaMemcpyAsync(d_leaves, leaves, n_leaves * 32, cudaMemcpyHostToDevice, s) != cudaSuccess) {
-                result = fail(PSD_ERR_CUDA, "leaf upload failed: %s", cudaGetErrorString(cudaGetLastError()));
-                break;
-            }
-            src = d_leaves;
-        }
-        uint32_t* bufs[2] = {scratch, scratch + half * 8};
-        int which = 0;
-        int src_repr = repr;
-        for (size_t pairs = half; pairs >= 1; pairs /= 2) {
-            SpongeArgs a = base_args(ctx, pairs);
-            a.in = src;
-            a.n_absorb = 2;
-            a.in_layout = kLayoutAos;
-            a.in_repr = src_repr;
-            a.do_squeeze = 1;
-            a.n_squeeze = 1;
-            a.out = bufs[which];
-            a.out_layout = kLayoutAos;
-            a.out_repr = pairs == 1 ? repr : kReprMontgomery;
-            result = launch(ctx, a, s);
+            result = merkle_upload_leaves(ctx, leaves, n_leaves, s, &src);
             if (result != PSD_OK) break;
-            src = bufs[which];
-            src_repr = kReprMontgomery;
-            which ^= 1;
-            if (pairs == 1) break;
         }
+        const uint32_t* d_root = nullptr;
+        result = merkle_reduce_async(ctx, src, repr, n_leaves, mem == PSD_MEM_DEVICE ? as_u32(root) : nullptr, repr, s, &d_root);
         if (result != PSD_OK) break;
-        const cudaMemcpyKind kind = mem == PSD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
-        if (cudaMemcpyAsync(root, src, 32, kind, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) {
+        if (mem == PSD_MEM_HOST && cudaMemcpyAsync(root, d_root, 32, cudaMemcpyDeviceToHost, s) != cudaSuccess) {
             result = fail(PSD_ERR_CUDA, "root download failed: %s", cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+        if (cudaStreamSynchronize(s) != cudaSuccess) {
+            result = fail(PSD_ERR_CUDA, "Merkle levels failed: %s", cudaGetErrorString(cudaGetLastError()));
             break;
         }
         result = check_err_flag(ctx, s);
@@ -1086,6 +1262,10 @@ struct psd_batch {
     cudaStream_t own_stream = nullptr;
     void* d_io = nullptr;          // device staging for host-side inputs/outputs
     size_t d_io_bytes = 0;
+    // this batch's own non-canonical-input flag, so that batches of one context used from different
+    // threads cannot steal or clear each other's
+    int32_t* d_err = nullptr;      // lives in the tail of the d_state allocation
+    int32_t h_err = 0;
 };
 
 namespace {
@@ -1104,6 +1284,7 @@ psd_status batch_io(psd_batch* b, size_t bytes) {
 }
 
 void batch_state_args(const psd_batch* b, SpongeArgs& a) {
+    a.err = b->d_err;
     a.state_in = b->d_state;
     a.state_in_layout = kLayoutSoa;
     a.state_in_repr = kReprMontgomery;
@@ -1129,7 +1310,7 @@ psd_status psd_batch_new(psd_ctx* ctx, size_t n, psd_batch** out) {
     ctx->refs.fetch_add(1);
     b->n = n;
     const size_t bytes = n * ctx->t * 32;
-    if (cudaMalloc(&b->d_state, bytes) != cudaSuccess) {
+    if (cudaMalloc(&b->d_state, bytes + 16) != cudaSuccess) {
         cudaGetLastError();
         ctx_release(ctx);
         delete b;
@@ -1137,7 +1318,8 @@ psd_status psd_batch_new(psd_ctx* ctx, size_t n, psd_batch** out) {
     }
     if (cudaStreamCreateWithFlags(&b->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         (b->stream = b->own_stream, false) ||
-        cudaMemsetAsync(b->d_state, 0, bytes, b->stream) != cudaSuccess ||   // vec![F::zero(); t], mod.rs:220
+        (b->d_err = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(b->d_state) + bytes), false) ||
+        cudaMemsetAsync(b->d_state, 0, bytes + 16, b->stream) != cudaSuccess ||   // vec![F::zero(); t], mod.rs:220
         cudaStreamSynchronize(b->stream) != cudaSuccess) {
         psd_status st = fail(PSD_ERR_CUDA, "batch init failed: %s", cudaGetErrorString(cudaGetLastError()));
         psd_batch_free(b);
@@ -1212,9 +1394,16 @@ psd_status psd_batch_absorb(psd_batch* b, const uint64_t* elems, uint32_t k, int
     a.in_repr = repr;
     st = launch(ctx, a, b->stream);
     if (st != PSD_OK) return st;
-    advance_mode(ctx->rate, k, false, 0, &b->mode, &b->index);
     PSD_CUDA(cudaStreamSynchronize(b->stream));
-    return repr == PSD_REPR_CANONICAL ? check_err_flag(ctx, b->stream) : PSD_OK;
+    if (repr == PSD_REPR_CANONICAL) {
+        // A rejected input leaves mode/index where they were (the reference would have panicked inside
+        // from_bigint before touching the sponge); the states of the batch are then unspecified and must
+        // be restored with psd_batch_set_state before it is used again.
+        st = read_err_flag(&b->h_err, b->d_err, b->stream);
+        if (st != PSD_OK) return st;
+    }
+    advance_mode(ctx->rate, k, false, 0, &b->mode, &b->index);
+    return PSD_OK;
 }
 
 static psd_status batch_squeeze(psd_batch* b, uint32_t k, uint64_t* out, uint8_t* out_bytes, uint32_t n_bytes, int layout,
@@ -1325,11 +1514,12 @@ psd_status psd_batch_set_state(psd_batch* b, const uint64_t* states, int layout,
     a.state_out = b->d_state;
     a.state_out_layout = kLayoutSoa;
     a.state_out_repr = kReprMontgomery;
+    a.err = b->d_err;
     st = launch(ctx, a, b->stream);
     if (st != PSD_OK) return st;
     PSD_CUDA(cudaStreamSynchronize(b->stream));
     if (repr == PSD_REPR_CANONICAL) {
-        st = check_err_flag(ctx, b->stream);
+        st = read_err_flag(&b->h_err, b->d_err, b->stream);
         if (st != PSD_OK) return st;
     }
     b->mode = mode;

@@ -39,6 +39,10 @@ struct SpongeArgs {
     uint8_t* out_bytes;
     uint32_t n_bytes;
     int32_t* err;           // device flag: set to 1 if a canonical input was >= p
+    // kernels of the shared-memory form only: the context's constant image in global memory (16-byte
+    // aligned, pool_words a multiple of 4); d's offsets are relative to it
+    const uint32_t* pool_img;
+    uint32_t pool_words;
 };
 
 struct LaunchCfg {

@@ -14,11 +14,23 @@ namespace psd {
 // 62 KiB of the 64 KiB constant bank, shared by all live contexts of a device (slot allocator on
 // the host side, see api.cu).
 constexpr uint32_t kConstPoolWords = 15872;
+// Largest constant image a kernel of the shared-memory form accepts (one block per SM may use up to
+// 227 KiB; the t = 5 variant-5 image is the largest in use at about 100 KiB).
+constexpr uint32_t kSmemPoolMaxWords = 56 * 1024;
 
+// Where the kernels of a translation unit read their constants from.  Default: the unit's slice of the
+// constant bank (uniform loads, operands in uniform registers).  With -DPSD_POOL_SHARED=1 the same code
+// is compiled against a dynamic shared-memory array that every block fills from the context's image in
+// global memory before its first permutation (sponge_kernel's prologue): no 62 KiB limit and no
+// competition between parameter sets, at the price of broadcast LDS reads into vector registers.
 #if defined(__CUDACC__)
-__constant__ __align__(16) uint32_t c_pool[kConstPoolWords];
+#if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
+extern __shared__ __align__(16) uint32_t c_pool[];
 #else
-alignas(16) static uint32_t c_pool[kConstPoolWords];
+__constant__ __align__(16) uint32_t c_pool[kConstPoolWords];
+#endif
+#else
+alignas(16) static uint32_t c_pool[kSmemPoolMaxWords];
 #endif
 
 // One field element (8 words) from the pool.  Offsets are multiples of 8 words, so this is two

@@ -82,11 +82,37 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // ran 162 M at 5, 6 and 7 resident blocks alike.
 #define PSD_KERNEL_MAX_BLOCK(VARIANT) ((VARIANT) == 5 ? 512 : 128)
 #define PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT) ((VARIANT) == 5 ? 1 : PSD_MIN_BLOCKS(T))
-template <class F, int T, int ALPHA, int VARIANT>
-__global__ void __launch_bounds__(PSD_KERNEL_MAX_BLOCK(VARIANT), PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT)) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+// Shared-memory form (POOL == 1): every block carries its own copy of the constant image, so blocks are
+// large -- variant 5 as above (512 threads, one block per SM), the integer variants 448 threads with two
+// blocks per SM (the 28 warps per SM that seven 128-thread blocks give the constant-bank form).
+#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 5 ? 512 : 448)
+#define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) == 5 ? 1 : 2)
+#if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
+#define PSD_POOL_KIND 1
+#define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_SMEM_BLOCK(VARIANT), PSD_SMEM_BLOCKS(VARIANT))
+#else
+#define PSD_POOL_KIND 0
+#define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_KERNEL_MAX_BLOCK(VARIANT), PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT))
+#endif
+// POOL is part of the kernel's name only so that the constant-bank and the shared-memory build of the same
+// (field, T, ALPHA, VARIANT) are different symbols; the code difference comes from how c_pool is declared
+// in the translation unit (poseidon_core.cuh).
+template <class F, int T, int ALPHA, int VARIANT, int POOL = PSD_POOL_KIND>
+__global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constant__ SpongeArgs a) {
+    static_assert(POOL == PSD_POOL_KIND, "POOL must match the translation unit's pool kind");
     const PermDesc& d = a.d;
     const uint32_t rate = d.rate, cap = d.capacity;
     bool bad = false;
+
+#if PSD_POOL_KIND == 1
+    {   // stage the context's constant image: global (L2-resident after the first blocks) -> shared
+        const uint4* src = reinterpret_cast<const uint4*>(a.pool_img);
+        uint4* dst = reinterpret_cast<uint4*>(c_pool);
+        const uint32_t n16 = a.pool_words >> 2;
+        for (uint32_t q = threadIdx.x; q < n16; q += blockDim.x) dst[q] = __ldg(src + q);
+        __syncthreads();
+    }
+#endif
 
     // One sponge per thread and an early exit -- deliberately NOT a grid-stride loop: inside a
     // (potentially divergent) per-thread loop ptxas stops using the uniform datapath, and every

@@ -22,6 +22,7 @@ typedef Bls12381Fr TuField;
 #define PSD_TU_FNAME "bls12_381"
 #endif
 
+#if PSD_POOL_KIND == 0
 static int tu_upload(uint32_t word_off, const uint32_t* words, uint32_t n_words, void* stream) {
     return (int)cudaMemcpyToSymbolAsync(c_pool, words, (size_t)n_words * 4, (size_t)word_off * 4,
                                         cudaMemcpyHostToDevice, (cudaStream_t)stream);
@@ -29,16 +30,25 @@ static int tu_upload(uint32_t word_off, const uint32_t* words, uint32_t n_words,
 
 // one pool for all widths of this unit: a parameter set fills most of it anyway
 static ConstPoolRegistrar g_pool(TuField::kFieldId, kFp52PoolKey, tu_upload);
+#define PSD_POOL_TAG ""
+#else
+#define PSD_POOL_TAG ",smem"
+#endif
 
 #define PSD_REG_FP52(T, ALPHA)                                                                 \
     static SpongeKernelRegistrar g_reg_##T##_##ALPHA(SpongeKernelEntry{                        \
-        TuField::kFieldId, T, ALPHA, 5, sponge_kernel<TuField, T, ALPHA, 5>,                   \
-        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5>"});
+        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, sponge_kernel<TuField, T, ALPHA, 5>,    \
+        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ">"});
 
 PSD_REG_FP52(3, 5)
 PSD_REG_FP52(3, 17)
 #if PSD_TU_FIELD == 0
 PSD_REG_FP52(2, 5)
+#endif
+// t = 5: the tables (about 96 KiB) exceed the constant bank, so this width exists in the shared-memory
+// form only
+#if PSD_POOL_KIND == 1 && PSD_TU_FIELD == 0
+PSD_REG_FP52(5, 5)
 #endif
 
 }  // namespace psd

@@ -208,6 +208,14 @@ class PoseidonContext:
         check(lib.psd_ctx_active_variant(self.handle, C.byref(v)))
         return v.value
 
+    def describe(self) -> dict:
+        """Which kernel a launch on this context runs and where its constants live (psd_ctx_describe)."""
+        info = L.PsdCtxInfo()
+        check(lib.psd_ctx_describe(self.handle, C.byref(info)))
+        return dict(variant=info.variant, constants_home="bank" if info.constants_home == L.CONSTANTS_BANK else "shared",
+                    image_bytes=info.image_bytes, image_shared_by=info.image_shared_by,
+                    kernel_name=info.kernel_name.decode())
+
     # -- host-array batch calls ---------------------------------------------------------------
     def permute_batch(self, states: np.ndarray, layout: int = L.LAYOUT_AOS, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
         """n independent `permute`s (mod.rs:95-118), in place on a uint64 array holding n*t elements."""

@@ -127,7 +127,7 @@ extern "C" int emu_permute(int field, uint32_t rate, uint32_t capacity, uint32_t
     if (variant == 4) append_digit_tables(*hf, t, rf, rp, mds, d, img);
     if (variant == 5) append_digit_tables(*hf, t, rf, rp, mds, d, img, true);
     if (variant == 6) append_fp52_tables(*hf, t, rf, rp, ark, mds, d, img);
-    if (img.size() > kConstPoolWords) return variant == 6 ? 1 : -2;   // variant 6: tables of wide states exceed the bank
+    if (img.size() > kSmemPoolMaxWords) return variant == 6 ? 1 : -2;   // the host model's pool has the shared-memory form's size
     memcpy(c_pool, img.data(), img.size() * 4);
     // fp52.cuh's host model is fma() under round-toward-zero (the device uses fma.rz.f64)
     const int old_round = fegetround();

@@ -9,7 +9,7 @@ from conftest import field_id, field_name, oracle_cfg, to_limbs
 
 pytestmark = pytest.mark.gpu
 
-NAMES = ["bn254_t3", "bn254_t2", "bn254_full_only", "bn254_rp1", "bn254_rp2_alpha17"]
+NAMES = ["bn254_t3", "bn254_t2", "bn254_full_only", "bn254_rp1", "bn254_rp2_alpha17", "bn254_t5"]
 
 
 @pytest.fixture(scope="module")
@@ -87,14 +87,18 @@ def test_fp52_sponge_calls(S, ref):
         ctx.close()
 
 
-def test_fp52_second_context_falls_back(S, ref):
+def test_fp52_second_context_keeps_the_variant(S, ref):
+    """The variant-5 constant pool holds one parameter set; the next one runs the same variant with its
+    tables staged through shared memory instead of dropping to an integer variant."""
+    import os
     oc, orc, ctx = make(S, ref, "bn254_t3")
     oc2, orc2, ctx2 = make(S, ref, "bn254_t2")
     try:
         ctx.set_variant(5)
         ctx2.set_variant(5)
-        assert ctx.active_variant() == 5
-        assert ctx2.active_variant() != 5      # the pool is taken; same results through another variant
+        assert ctx.active_variant() == 5 and ctx2.active_variant() == 5
+        if os.environ.get("PSD_FORCE_SMEM") != "1":
+            assert ctx.describe()["constants_home"] == "bank" and ctx2.describe()["constants_home"] == "shared"
         st = orc2.synth(64 * 2, seed=3, montgomery=True)
         assert np.array_equal(ctx2.permute_batch(st.copy()), orc2.permute_batch(st.copy()))
     finally:
