@@ -16,7 +16,11 @@ The JSON line carries `roofline` (integer-multiply pipe: algorithmic 32x32 multi
 permutation x permutations / kernel time, against the K0 probe measured in the same run; the HBM
 view is given next to it), `cpu_baseline` (the C port of the reference's CPU path, oracle/, on the
 host cores, bounded sample), `e2e` (same metric through psd_permute_batch with pinned HOST
-buffers: H2D + kernel + D2H inside the timed region), `clocks`, and `gpu_launches`.
+buffers: H2D + kernel + D2H inside the timed region; next to it `copy_ceiling_gbs`, the rate of the same
+copies with no kernel, all ranks at once), `clocks`, and `gpu_launches`.  At N > 1 rank 0 appends a `merkle`
+sub-record: ONE tree over N x 2^23 leaves through psd_merkle_root_multi (one process driving all N GPUs,
+32-byte roots gathered with peer copies), its time, its efficiency against one 2^23-leaf subtree on one GPU,
+and `root_ok`.
 """
 import argparse
 import json
@@ -70,6 +74,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target duration of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
+    ap.add_argument("--no-merkle", action="store_true", help="skip the multi-GPU Merkle sub-record at N > 1")
     return ap.parse_args()
 
 
@@ -234,6 +239,130 @@ def bind_to_gpu_numa_node(local_rank):
     return None
 
 
+def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
+    """What the kernel that ran really executes, from two files written by tools, never typed in here:
+      sponge_b200/lib/kernel_sass.json   build time (tools/kernel_sass.py): SASS fingerprint + static instruction mix;
+      profiles/kernel_counts.json        tools/ncu_counts.py over a committed `ncu --set full` capture: dynamic warp
+                                         instructions per permutation by pipe, registers, DRAM bytes per launch.
+    The ncu numbers are used only if their SASS fingerprint equals this build's kernel (else `stale`).  From them
+    and THIS run's time and clock:  issue_frac = warp instructions issued / issue slots, and
+    heavy_pipe_frac = (4 N_imad_wide + 2 N_imad + 2 N_fp64) warp-cycles / cycles -- the share of the time the
+    half-rate multiplier datapaths (integer multiply, FP64) are busy under the cycle model of DESIGN.md section 4.
+    Returns (exec dict, dram bytes per launch or None)."""
+    import re
+    info = ctx.describe()
+    out = dict(kernel=info["kernel_name"], constants_home=info["constants_home"])
+    m = re.match(r"sponge_kernel<(\w+),t=(\d+),alpha=(\d+),variant=(\d+)(,smem)?>", info["kernel_name"])
+    if not m:
+        return out, None
+    fld = "Bn254Fr" if m.group(1) == "bn254" else "Bls12381Fr"
+    key = (f"void psd::sponge_kernel<psd::{fld}, (int){m.group(2)}, (int){m.group(3)}, (int){m.group(4)}, "
+           f"(int){1 if m.group(5) else 0}>(psd::SpongeArgs)")
+    sass = {}
+    try:
+        sass = json.load(open(os.path.join(ROOT, "sponge_b200", "lib", "kernel_sass.json")))
+    except (OSError, ValueError):
+        pass
+    srec = sass.get(key)
+    if srec:
+        straight = [l for l in srec["loops"] if not l["has_inner_loop"]]
+        straight.sort(key=lambda l: -l["total"])
+        out["sass_sha256"] = srec["sass_sha256"][:16]
+        out["static_instructions"] = srec["instructions"]["total"]
+        if straight:
+            out["largest_straight_line_loop"] = {k: straight[0][k] for k in ("total", "imad_wide", "imad_hi", "imad", "fp64",
+                                                                             "iadd3", "lds", "ldc")}
+    counts = {}
+    try:
+        counts = json.load(open(os.path.join(ROOT, "profiles", "kernel_counts.json")))
+    except (OSError, ValueError):
+        pass
+    crec = counts.get(key)
+    traffic = None
+    if crec:
+        fresh = bool(srec) and crec.get("sass_sha256") == srec["sass_sha256"]
+        out["ncu_capture"] = crec.get("source")
+        out["ncu_capture_matches_this_build"] = fresh
+        per = crec.get("warp_inst_per_perm", {})
+        out["warp_inst_per_perm"] = per
+        out["registers_per_thread"] = crec.get("registers_per_thread")
+        sm_mhz = (clocks or {}).get("sm_mhz") or crec.get("sm_mhz")
+        if per and sm_mhz:
+            sm_count = crec.get("sm_count", 148)
+            cycles = ms_per_step * 1e-3 * sm_mhz * 1e6                   # per SM sub-partition, this run
+            warp_perms = perms_per_step_gpu / 32.0 / (sm_count * 4)         # per SM sub-partition
+            heavy = 4 * per.get("imad_wide", 0) + 2 * per.get("imad", 0) + 2 * per.get("fp64", 0)
+            out["issue_frac"] = per.get("total", 0) * warp_perms / cycles
+            out["heavy_pipe_frac"] = heavy * warp_perms / cycles
+            out["w_exec_imul_per_perm"] = per.get("imad_wide", 0) + per.get("imad", 0)
+            out["fp64_inst_per_perm"] = per.get("fp64", 0)
+        if crec.get("workload") == name and crec.get("log_n") == log_n and fresh:
+            traffic = crec.get("dram_bytes_per_launch")
+    return out, traffic
+
+
+def multi_gpu_merkle(S, cfg, n_gpus, args, log_leaves=23):
+    """configs[3] through psd_merkle_root_multi: one process, n_gpus devices, 2^log_leaves leaves per device.
+    Wall clock around the blocking call (it returns when the root is on device 0), median of `steps` calls after
+    warm-up; the single-device time of one subtree is measured the same way for the efficiency.  root_ok: the
+    multi-device root equals the single-device root over the n_gpus subtree roots, each computed by its own device
+    with psd_merkle_root (the oracle comparison of the same entry points lives in tests/test_gpu_multi.py)."""
+    import torch
+    per = 1 << log_leaves
+    mc = S.MultiContext(cfg, list(range(n_gpus)))
+    try:
+        bufs, subs, streams = [], [], []
+        for d in range(n_gpus):
+            with torch.cuda.device(d):
+                b = torch.empty((per, 4), dtype=torch.int64, device=f"cuda:{d}")
+                s = torch.cuda.current_stream(d).cuda_stream
+                mc.ctxs[d].synth_fill_dev(b.data_ptr(), per, 0xC4, first_index=d * per, stream=s)
+                mc.ctxs[d].synchronize(s)
+                bufs.append(b)
+                streams.append(s)
+                subs.append(torch.zeros((1, 4), dtype=torch.int64, device=f"cuda:{d}"))
+        root = torch.zeros((1, 4), dtype=torch.int64, device="cuda:0")
+        ptrs = [b.data_ptr() for b in bufs]
+        steps = max(3, min(args.steps, 10))
+
+        def timed(fn):
+            for _ in range(3):
+                fn()
+            ts = []
+            for _ in range(steps):
+                t0 = time.perf_counter()
+                fn()
+                ts.append((time.perf_counter() - t0) * 1e3)
+            ts.sort()
+            return ts[len(ts) // 2], ts[0]
+        l0 = S.kernel_launch_count()
+        multi_ms, multi_best = timed(lambda: mc.merkle_root_dev(ptrs, per, root.data_ptr(), streams=streams))
+        launches = (S.kernel_launch_count() - l0) // (steps + 3)
+
+        def single():
+            mc.ctxs[0].merkle_root_dev(ptrs[0], per, subs[0].data_ptr(), stream=streams[0])   # blocks until written
+        single_ms, single_best = timed(single)
+        # root check
+        for d in range(n_gpus):
+            with torch.cuda.device(d):
+                mc.ctxs[d].merkle_root_dev(ptrs[d], per, subs[d].data_ptr(), stream=streams[d])
+        gathered = torch.cat([x.to("cuda:0") for x in subs])
+        top = torch.zeros((1, 4), dtype=torch.int64, device="cuda:0")
+        with torch.cuda.device(0):
+            mc.ctxs[0].merkle_root_dev(gathered.data_ptr(), n_gpus, top.data_ptr(), stream=streams[0])
+        root_ok = bool(torch.equal(top.cpu(), root.cpu()))
+        compressions = n_gpus * per - 1
+        return dict(workload=f"c4: ONE Poseidon Merkle tree over {n_gpus} x 2^{log_leaves} BN254 leaves, per-GPU subtrees, "
+                             f"{n_gpus} roots gathered with peer copies, top levels on device 0 (psd_merkle_root_multi, "
+                             "one process)",
+                    n_gpus=n_gpus, leaves=n_gpus * per, ms_per_tree=multi_ms, ms_per_tree_best=multi_best,
+                    ms_single_subtree_one_gpu=single_ms, efficiency_vs_one_gpu=single_ms / multi_ms,
+                    compressions_per_s=compressions / (multi_ms * 1e-3), root_ok=root_ok, launches_per_tree=int(launches),
+                    timing="host wall clock around the blocking call, median of %d" % steps)
+    finally:
+        mc.close()
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
@@ -266,7 +395,11 @@ def main():
                     n_gpus=args.gpus, steps=args.steps, warmup=args.warmup, ms_per_step=1e3 * sum(secs) / len(secs),
                     higher_is_better=True,
                     scaling="weak", vs_baseline=None, dtype="u32x8 (256-bit Montgomery, 4x64-bit limbs on CPU)",
-                    data="synthetic", config=dict(workload=f"{name}: {w['desc']}", sample=best["sample"]),
+                    data="synthetic",
+                    # the same `config` as the product arm names; each step times a bounded sample of that workload on
+                    # all host threads and reports the per-unit rate (cpu_baseline.sample says how large)
+                    config=dict(workload=f"{name}: {w['desc']}"),
+                    note="CPU arm: per-unit rate over a bounded sample of the workload per step -- " + best["sample"],
                     cpu_baseline=best,
                     e2e=dict(value=value, unit="perm/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
         print(json.dumps(line))
@@ -313,36 +446,30 @@ def main():
         launches_per_step = 1
         alg_bytes = n * 5 * 32
     elif name == "c4":
+        from sponge_b200.distributed import distributed_merkle_root_dev
         buf = torch.empty((n, 4), dtype=torch.int64, device="cuda")
-        root = torch.empty((1, 4), dtype=torch.int64, device="cuda")
         ctx.synth_fill_dev(buf.data_ptr(), n, seed, first, stream=sptr)
-        roots = torch.empty((world, 4), dtype=torch.int64, device="cuda") if world > 1 else None
+        roots = torch.empty((world + 1, 4), dtype=torch.int64, device="cuda")
         top = torch.empty((1, 4), dtype=torch.int64, device="cuda")
 
         def step():
-            ctx.merkle_root_dev(buf.data_ptr(), n, root.data_ptr(), stream=sptr)
-            if world > 1:
-                # the one exchange step of the path: world x 32-byte subtree roots to every rank
-                dist.all_gather_into_tensor(roots, root)
-                if rank == 0:
-                    ctx.merkle_root_dev(roots.data_ptr(), world, top.data_ptr(), stream=sptr)
+            # per-rank subtree; at N > 1 the one exchange step of the path (world x 32-byte roots, all-gather)
+            # and the top levels -- sponge_b200/distributed.py, nothing touches the host
+            distributed_merkle_root_dev(ctx, buf.data_ptr(), n, roots, top, stream=sptr)
         launches_per_step = log_n
         alg_bytes = n * 32 * 3 // 2
     else:
-        chunk = 64   # elements absorbed per call; inputs regenerated on the device chunk by chunk
-        buf = torch.empty((n * chunk, 4), dtype=torch.int64, device="cuda")
+        # 2^20 sponges x 1024 DISTINCT elements each, resident in HBM (32 GiB at the full size): one call,
+        # one launch, 512 permutations per sponge
+        k_absorb = 1024
+        buf = torch.empty((n * k_absorb, 4), dtype=torch.int64, device="cuda")
         outb = torch.empty((n, 32), dtype=torch.uint8, device="cuda")
-        ctx.synth_fill_dev(buf.data_ptr(), n * chunk, seed, first * chunk, stream=sptr)
+        ctx.synth_fill_dev(buf.data_ptr(), n * k_absorb, seed, first * k_absorb, stream=sptr)
 
         def step():
-            b = S.SpongeBatch(ctx, n)
-            b.set_stream(sptr)
-            for _ in range(1024 // chunk):
-                b.absorb_dev(buf.data_ptr(), chunk)
-            b.squeeze_bytes_dev(32, outb.data_ptr())
-            b.free()
-        launches_per_step = 1024 // chunk + 1
-        alg_bytes = n * 1024 * 32
+            ctx.absorb_squeeze_bytes_batch_dev(buf.data_ptr(), n, k_absorb, 32, outb.data_ptr(), stream=sptr)
+        launches_per_step = 1
+        alg_bytes = n * (k_absorb * 32 + 32)
     ctx.synchronize(sptr)
 
     def barrier():
@@ -390,7 +517,7 @@ def main():
     if not args.no_e2e and name in ("c2", "c3"):
         in_el = n * t if name == "c2" else n * 4
         out_el = n * t if name == "c2" else n
-        h_in = torch.empty((in_el, 4), dtype=torch.int64).pin_memory()
+        h_in = torch.empty((in_el, 4), dtype=torch.int64).pin_memory()   # first touched by the rank that uses it
         h_in.copy_(buf.cpu())
         h_out = h_in if name == "c2" else torch.empty((out_el, 4), dtype=torch.int64).pin_memory()
         a_in = h_in.numpy().view(np.uint64)
@@ -415,10 +542,54 @@ def main():
             tt = torch.tensor([dt], device="cuda")
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
+        # copy ceiling: the SAME pinned buffers and chunk size, bare cudaMemcpyAsync H2D on one stream and D2H on
+        # another, no kernel, all ranks at once -- what the box's host<->device path gives this access pattern
+        chunk_el = (1 << 17) * (t if name == "c2" else 4)
+        out_chunk_el = (1 << 17) * (t if name == "c2" else 1)
+        d_in = buf
+        d_out = buf if name == "c2" else out
+        s_h2d, s_d2h = torch.cuda.Stream(), torch.cuda.Stream()
+
+        def copy_pass():
+            for c0 in range(0, in_el, chunk_el):
+                with torch.cuda.stream(s_h2d):
+                    d_in[c0:c0 + chunk_el].copy_(h_in[c0:c0 + chunk_el], non_blocking=True)
+            for c0 in range(0, out_el, out_chunk_el):
+                with torch.cuda.stream(s_d2h):
+                    h_out[c0:c0 + out_chunk_el].copy_(d_out[c0:c0 + out_chunk_el], non_blocking=True)
+            s_h2d.synchronize()
+            s_d2h.synchronize()
+        copy_pass()
+        barrier()
+        c0t = time.perf_counter()
+        for _ in range(e2e_steps):
+            copy_pass()
+        cdt = time.perf_counter() - c0t
+        if dist is not None:
+            tt = torch.tensor([cdt], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            cdt = float(tt.item())
+        step_bytes = (in_el + out_el) * 32
+        ceiling_gbs = step_bytes * world * e2e_steps / cdt / 1e9
+        e2e_gbs = step_bytes * world * e2e_steps / dt / 1e9
         e2e = dict(value=units * world * e2e_steps / dt, unit="perm/s", h2d_bytes_per_step=in_el * 32,
                    d2h_bytes_per_step=out_el * 32, steps=e2e_steps,
-                   note="psd_permute_batch/psd_absorb_squeeze_batch with PSD_MEM_HOST on pinned buffers; "
-                        "wall clock around blocking calls", numa_node=numa_node)
+                   host_device_gbs=e2e_gbs, copy_ceiling_gbs=ceiling_gbs, frac_of_ceiling=e2e_gbs / ceiling_gbs,
+                   frac_of_device_rate=(units * world * e2e_steps / dt) / value,
+                   note="psd_permute_batch/psd_absorb_squeeze_batch with PSD_MEM_HOST on pinned buffers; wall clock around "
+                        "blocking calls.  copy_ceiling_gbs = aggregate H2D+D2H GB/s of bare cudaMemcpyAsync over the same "
+                        "pinned buffers in the same 2^17-sponge chunks on two streams with no kernel, all ranks at once; "
+                        "frac_of_ceiling = this leg's own host<->device GB/s over that",
+                   numa_node=numa_node)
+        del h_in, h_out
+
+    # ---- N > 1: ONE Merkle tree over all GPUs through the C ABI (rank 0 drives every device) ----------------
+    merkle = None
+    if world > 1 and not args.no_merkle:
+        barrier()
+        if rank == 0:
+            merkle = multi_gpu_merkle(S, cfg, world, args)
+        barrier()
 
     if rank != 0:
         if dist is not None:
@@ -442,35 +613,19 @@ def main():
     # this run.  IMAD.WIDE.U32 (the 32x32->64 form a multi-limb product needs) issues at less than half
     # of that on B200 (k0.imad_wide_per_s), so a kernel that executes all W_alg multiplies as IMAD.WIDE
     # tops out near 0.45; the optimised kernel gets above that by executing fewer multiplies than W_alg.
-    # DRAM bytes per launch from the committed ncu --set full capture of this exact workload
-    # (profiles/r1c_c2_v5_summary.md: dram__bytes_read.sum + dram__bytes_write.sum); algorithmic = 3.22 GB.
-    traffic = 3.196e9 if (name == "c2" and log_n == 24) else None
     active_variant = ctx.active_variant()
-    # Executed work and pipe activity of the kernel that ran, for c2, from the committed ncu captures:
-    #   variant 5 (profiles/r1c_c2_v5_summary.md): integer multiplies only in the S-boxes and the Montgomery
-    #   quotient digits; the linear layer is 10 415 exact 52x52-bit products on the FP64 pipe (3 FP64
-    #   instructions each).  The three pipes overlap little on B200.
-    #   variant 3 (profiles/r1_c2_final_summary.md): all-integer, 56 625 multiplies, fmaheavy 89.5 % active.
-    if name == "c2" and active_variant == 5:
-        exec_info = dict(w_exec_imul_per_perm=29346, fp64_products_per_perm=10415, fmaheavy_active_pct_ncu=54.5,
-                         fp64_active_pct_ncu=30.7, alu_active_pct_ncu=40.4, issue_active_pct_ncu=55.1,
-                         note="frac > 1 is not a measurement error: achieved counts the reference's 112 608 "
-                              "algorithmic 32x32 multiplies per permutation, of which this kernel executes 29 346 on "
-                              "the integer multiplier and replaces the rest by 10 415 exact 52x52-bit products on "
-                              "the FP64 pipe; the kernel is bound by instruction issue (DESIGN.md section 7)")
-    elif name == "c2" and active_variant == 3:
-        exec_info = dict(w_exec_imul_per_perm=56625, fp64_products_per_perm=0, fmaheavy_active_pct_ncu=89.5,
-                         fp64_active_pct_ncu=0.0, alu_active_pct_ncu=38.2, issue_active_pct_ncu=47.8)
-    else:
-        exec_info = dict(w_exec_imul_per_perm=None, fmaheavy_active_pct_ncu=None)
+    exec_info, traffic = executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks)
     roofline = dict(bound="imad", achieved=achieved_imul / 1e9, peak=imad_lo / 1e9, unit="Gimul/s",
                     frac=achieved_imul / imad_lo, traffic=traffic,
+                    frac_is="useful-work ratio: the reference's ALGORITHMIC multiplies per second over the 32-bit IMAD "
+                            "issue rate; the kernel executes fewer multiplies than that (exec.*), so values above 1 are "
+                            "possible -- exec.heavy_pipe_frac and exec.issue_frac are the utilisation figures",
                     w_alg_imul_per_perm=w_alg, modmul_per_perm=mm,
                     # achieved = ALGORITHMIC multiplies (the reference's operation count) per
                     # second; the shipped kernels execute fewer (sparse partial rounds, constant products through
                     # tables, dedicated squaring), which is how frac can pass the 0.5 that
                     # IMAD.WIDE's half rate would otherwise impose
-                    **exec_info,
+                    exec=exec_info,
                     peak_source="K0 probe in this run: sustained 32-bit IMAD results/s on all SMs "
                                 "(integer-multiply pipe issue rate)",
                     k0=dict(imad_wide_per_s=imad_wide, imad_lo_per_s=imad_lo, mont_mul_per_s=modmul_rate,
@@ -491,8 +646,12 @@ def main():
                             permutations_per_unit=perms_per_unit, kernel_variant=ctx.active_variant(), kernel_variant_requested=args.variant,
                             layout="AoS Montgomery, device-resident, in place",
                             l2="inputs larger than L2 (no flush needed)" if alg_bytes > (252 << 20) else "inputs fit L2",
-                            per_step_ms=[round(x, 4) for x in per_step_ms]),
+                            per_step_ms=[round(x, 4) for x in per_step_ms],
+                            ms_per_step_median=sorted(per_step_ms)[len(per_step_ms) // 2], ms_per_step_best=min(per_step_ms),
+                            value_is="units x ranks / (max-over-ranks total device time / steps), i.e. the mean step"),
                 roofline=roofline, cpu_baseline=cpu, e2e=e2e, clocks=clocks, gpu_launches=int(launches))
+    if merkle is not None:
+        line["merkle"] = merkle
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

@@ -56,6 +56,9 @@ for p in "${pids[@]:-}"; do [[ -n "$p" ]] && { wait "$p" || fail=1; }; done
 OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o"
 for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o $OBJ/tu_${f}_${t}_smem.o"; done; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $LIB/libposeidon_b200.so $OBJS -Xcompiler -fPIC
+# static facts about the hot kernels (SASS fingerprints + instruction mix) for bench.py's roofline block
+python3 tools/kernel_sass.py $LIB/kernel_sass.json $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/tu_0_3.o $OBJ/tu_0_3_smem.o \
+  $OBJ/tu_0_5.o $OBJ/tu_0_5_smem.o $OBJ/tu_1_3.o $OBJ/tu_1_3_smem.o
 # CPU oracle (test infrastructure)
 if newer oracle/liboracle.so oracle/poseidon_oracle.c; then
   gcc -O3 -fopenmp -shared -fPIC -o oracle/liboracle.so oracle/poseidon_oracle.c

@@ -133,6 +133,16 @@ psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, 
                                           uint32_t n_absorb, uint32_t n_bytes, uint8_t* outputs,
                                           int layout, int repr, int mem, void* stream);
 
+/* Ragged form: sponge i absorbs the elements inputs[offsets[i] .. offsets[i+1]) (AoS, concatenated;
+ * offsets has n+1 entries, offsets[0] = 0, non-decreasing; a sponge may absorb nothing) and then squeezes
+ * n_squeeze elements -- what the reference's callers do when they absorb lists of differing lengths into
+ * different sponges (src/poseidon/tests.rs:45-69; AbsorbWithLength, absorb.rs:82-101).  Same kernel variant
+ * as the lock-step calls, in a form whose warps tolerate differing lengths; sort or bucket by length on the
+ * caller's side if the lengths vary widely (a warp takes as long as its longest sponge).  outputs: n*n_squeeze
+ * elements.  mem = PSD_MEM_DEVICE: inputs, offsets and outputs are device pointers. */
+psd_status psd_absorb_squeeze_ragged_batch(psd_ctx* ctx, const uint64_t* inputs, const uint64_t* offsets, size_t n,
+                                           uint32_t n_squeeze, uint64_t* outputs, int repr, int mem, void* stream);
+
 /* Merkle root over n_leaves (a power of two) with the 2-to-1 compression
  *   H(l, r) := { s = PoseidonSponge::new; s.absorb(&[l, r]); s.squeeze_native_field_elements(1)[0] }
  * (rate >= 2).  leaves: n_leaves elements (AoS); root: 1 element.  Intermediate levels live in a
@@ -181,6 +191,32 @@ psd_status psd_compress_pairs(psd_ctx* ctx, const uint64_t* in, size_t n_pairs, 
 #define PSD_NOALLOC_MAX_LEAVES 65536
 psd_status psd_merkle_root_noalloc(psd_ctx* ctx, const uint64_t* leaves, size_t n_leaves, uint64_t* root, int repr,
                                    void* stream);
+
+/* ---- one process, several GPUs ------------------------------------------------------------------
+ * No counterpart in the reference, which leaves spreading independent sponges over workers to the
+ * caller (a sponge is a plain value: poseidon/mod.rs:44-60).  ctxs[0..n_gpus) are contexts created from
+ * the SAME psd_params on different devices (checked).  The batch calls take HOST buffers holding the
+ * whole batch and give device g the contiguous range psd_shard_range(n, g, n_gpus): every device runs
+ * its own upload / kernel / download pipeline from its own host thread, there is no exchange between
+ * devices, and the calls return when all outputs are in host memory.  Layout/repr as in the
+ * single-device calls (SoA shards are strided sub-blocks of the caller's arrays). */
+void psd_shard_range(size_t n, int rank, int world, size_t* lo, size_t* hi);
+psd_status psd_permute_batch_multi(psd_ctx* const* ctxs, int n_gpus, uint64_t* states, size_t n, int layout,
+                                   int repr);
+psd_status psd_absorb_squeeze_batch_multi(psd_ctx* const* ctxs, int n_gpus, const uint64_t* inputs, size_t n,
+                                          uint32_t n_absorb, uint32_t n_squeeze, uint64_t* outputs, int layout,
+                                          int repr);
+/* Merkle root of the tree whose leaves are leaves_per_gpu[0] || leaves_per_gpu[1] || ... (n_gpus and
+ * leaves_per_gpu_n powers of two; same H as psd_merkle_root).  Device g reduces its own subtree on its
+ * own stream; the only exchange is the n_gpus subtree roots (32 bytes each), copied with
+ * cudaMemcpyPeerAsync into a buffer in the first device's OWN memory, where that device hashes the top
+ * log2(n_gpus) levels.  mem = PSD_MEM_DEVICE: leaves_per_gpu[g] is a device pointer on ctxs[g]'s device,
+ * root a device pointer on ctxs[0]'s device, and streams (NULL, or n_gpus CUDA streams, one per device)
+ * are the streams the leaves were produced on.  mem = PSD_MEM_HOST: all host pointers (they may point
+ * into one contiguous array).  Returns when the root has been written. */
+psd_status psd_merkle_root_multi(psd_ctx* const* ctxs, int n_gpus, const uint64_t* const* leaves_per_gpu,
+                                 size_t leaves_per_gpu_n, uint64_t* root, int repr, int mem,
+                                 void* const* streams);
 
 /* ---- lock-step batch of sponges (absorb/squeeze bookkeeping lifted to batch) --------------------
  * A psd_batch is n PoseidonSponge<F> values that always receive calls of identical shape, so they

@@ -6,6 +6,7 @@ from ._lib import (LAYOUT_AOS, LAYOUT_SOA, MEM_DEVICE, MEM_HOST, REPR_CANONICAL,
 from .poseidon import (DuplexSpongeMode, FieldElementSize, PoseidonConfig, PoseidonContext,  # noqa: F401
                        PoseidonParameters, PoseidonSponge, PoseidonSpongeState, SpongeBatch,
                        find_poseidon_ark_and_mds, get_default_poseidon_parameters, ints_to_limbs,
+                       MultiContext, shard_range,
                        kernel_launch_count, limbs_to_ints, MODULUS, MODULUS_BIT_SIZE)
 
 from . import absorb  # noqa: F401,E402

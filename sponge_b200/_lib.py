@@ -80,11 +80,16 @@ _PROTOS = {
     "psd_permute_batch": (_i, [_vp, _vp, _sz, _i, _i, _i, _vp]),
     "psd_absorb_squeeze_batch": (_i, [_vp, _vp, _sz, _u32, _u32, _vp, _i, _i, _i, _vp]),
     "psd_absorb_squeeze_bytes_batch": (_i, [_vp, _vp, _sz, _u32, _u32, _vp, _i, _i, _i, _vp]),
+    "psd_absorb_squeeze_ragged_batch": (_i, [_vp, _vp, _vp, _sz, _u32, _vp, _i, _i, _vp]),
     "psd_merkle_root": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
     "psd_merkle_tree": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
     "psd_merkle_path": (_i, [_vp, _vp, _sz, _sz, _vp]),
     "psd_compress_pairs": (_i, [_vp, _vp, _sz, _vp, _i, _i, _vp]),
     "psd_merkle_root_noalloc": (_i, [_vp, _vp, _sz, _vp, _i, _vp]),
+    "psd_shard_range": (None, [_sz, _i, _i, C.POINTER(_sz), C.POINTER(_sz)]),
+    "psd_permute_batch_multi": (_i, [_pp, _i, _vp, _sz, _i, _i]),
+    "psd_absorb_squeeze_batch_multi": (_i, [_pp, _i, _vp, _sz, _u32, _u32, _vp, _i, _i]),
+    "psd_merkle_root_multi": (_i, [_pp, _i, _pp, _sz, _vp, _i, _i, _pp]),
     "psd_batch_new": (_i, [_vp, _sz, _pp]),
     "psd_batch_clone": (_i, [_vp, _pp]),
     "psd_batch_free": (None, [_vp]),

@@ -74,11 +74,11 @@ void register_sponge_kernel(const SpongeKernelEntry& e) { sponge_kernels().push_
 // whose table requirements the descriptor meets (variant 3 reads the full digit tables, 4 the lane-update
 // ones, 1-2 the regrouped constants, 5 the 52-bit-limb tables).
 static const SpongeKernelEntry* find_kernel(int field, int t, uint64_t alpha, int variant, int pool,
-                                            const PermDesc* d = nullptr) {
+                                            const PermDesc* d = nullptr, int ragged = 0) {
     const SpongeKernelEntry* best = nullptr;
     int best_score = -1;
     for (const auto& e : sponge_kernels()) {
-        if (e.field != field || e.t != t || e.pool != pool) continue;
+        if (e.field != field || e.t != t || e.pool != pool || e.ragged != ragged) continue;
         if (e.alpha != 0 && e.alpha != alpha) continue;
         if (e.variant > variant) continue;
         if (d) {
@@ -260,6 +260,10 @@ struct psd_ctx {
     size_t merkle_scratch_bytes = 0;
     void* merkle_leaves = nullptr;   // device copy of host leaves
     size_t merkle_leaves_bytes = 0;
+    // psd_merkle_root_multi: on the first context of a call, the gathered subtree roots (this device's own
+    // memory); on every context, the event that says "my root has arrived there"
+    void* multi_roots = nullptr;
+    cudaEvent_t multi_event = nullptr;
 };
 
 namespace {
@@ -368,10 +372,10 @@ struct Resolved {
     const Placement* pl = nullptr;
     const PermDesc* d = nullptr;
 };
-Resolved resolve_kernel(const psd_ctx* ctx) {
+Resolved resolve_kernel(const psd_ctx* ctx, int ragged = 0) {
     Resolved r;
     if (ctx->variant >= 5 && ctx->pl_fp && ctx->fdesc.fp_ok) {
-        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 5, ctx->pl_fp->kind, &ctx->fdesc);
+        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 5, ctx->pl_fp->kind, &ctx->fdesc, ragged);
         if (k && k->variant == 5) {
             r.k = k, r.pl = ctx->pl_fp, r.d = &ctx->fdesc;
             return r;
@@ -379,7 +383,7 @@ Resolved resolve_kernel(const psd_ctx* ctx) {
     }
     if (!ctx->pl_int) return r;
     const int want = std::min(ctx->variant, 4);
-    r.k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, want, ctx->pl_int->kind, &ctx->desc);
+    r.k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, want, ctx->pl_int->kind, &ctx->desc, ragged);
     r.pl = ctx->pl_int, r.d = &ctx->desc;
     return r;
 }
@@ -388,7 +392,7 @@ Resolved resolve_kernel(const psd_ctx* ctx) {
 std::atomic<uint64_t> g_smem_attr_done[512];
 
 psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
-    const Resolved r = resolve_kernel(ctx);
+    const Resolved r = resolve_kernel(ctx, a.in_offsets ? 1 : 0);
     const SpongeKernelEntry* k = r.k;
     if (!k) return fail(PSD_ERR_UNSUPPORTED, "no kernel for field %d, t=%u", ctx->field, ctx->t);
     if (a.n == 0) return PSD_OK;
@@ -928,6 +932,8 @@ static void ctx_teardown(psd_ctx* ctx) {
         if (ctx->h_err) cudaFreeHost(ctx->h_err);
         if (ctx->merkle_scratch) cudaFree(ctx->merkle_scratch);
         if (ctx->merkle_leaves) cudaFree(ctx->merkle_leaves);
+        if (ctx->multi_roots) cudaFree(ctx->multi_roots);
+        if (ctx->multi_event) cudaEventDestroy(ctx->multi_event);
         placement_release(ctx->pl_int);
         placement_release(ctx->pl_fp);
     }
@@ -1835,3 +1841,315 @@ extern "C" psd_status psd_merkle_root_noalloc(psd_ctx* ctx, const uint64_t* leav
     }
     return PSD_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Ragged batches: every sponge absorbs its own number of elements.
+// ------------------------------------------------------------------------------------------------
+extern "C" psd_status psd_absorb_squeeze_ragged_batch(psd_ctx* ctx, const uint64_t* inputs, const uint64_t* offsets, size_t n,
+                                                      uint32_t n_squeeze, uint64_t* outputs, int repr, int mem, void* stream) {
+    if (!ctx) return fail(PSD_ERR_ARG, "null context");
+    if (!valid_enum(repr, 1) || !valid_enum(mem, 1)) return fail(PSD_ERR_ARG, "bad repr/mem value");
+    if (n == 0) return PSD_OK;
+    if (!offsets) return fail(PSD_ERR_ARG, "null offsets");
+    if (n_squeeze && !outputs) return fail(PSD_ERR_ARG, "null output buffer");
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", ctx->device);
+    auto fill = [&](SpongeArgs& a, const uint32_t* d_in, const uint64_t* d_off, uint64_t base, uint32_t* d_out) {
+        a.in = d_in;
+        a.in_offsets = d_off;
+        a.in_offset_base = base;
+        a.in_layout = kLayoutAos;
+        a.in_repr = repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = n_squeeze;
+        a.out = d_out;
+        a.out_layout = kLayoutAos;
+        a.out_repr = repr;
+    };
+    if (mem == PSD_MEM_DEVICE) {
+        // offsets and inputs are device pointers; nothing can be validated on the host
+        if (!inputs) return fail(PSD_ERR_ARG, "null inputs");
+        SpongeArgs a = base_args(ctx, n);
+        fill(a, as_u32(inputs), offsets, 0, as_u32(outputs));
+        return launch(ctx, a, (cudaStream_t)stream);
+    }
+    // host: validate the offsets, then stage sponge ranges of at most ~128 MiB of input each
+    if (offsets[0] != 0) return fail(PSD_ERR_ARG, "offsets[0] must be 0");
+    for (size_t i = 0; i < n; i++) {
+        if (offsets[i + 1] < offsets[i]) return fail(PSD_ERR_ARG, "offsets must be non-decreasing (index %zu)", i + 1);
+        if (offsets[i + 1] - offsets[i] > 0xffffffffull) return fail(PSD_ERR_ARG, "sponge %zu absorbs too many elements", i);
+    }
+    if (offsets[n] && !inputs) return fail(PSD_ERR_ARG, "null inputs");
+    std::lock_guard<std::mutex> lk(ctx->stage_mu);
+    const uint64_t max_el = (128ull << 20) / 32;
+    const size_t max_sponges = 1u << 17;
+    int slot = 0;
+    psd_status st = PSD_OK;
+    size_t first = 0;
+    // chunk boundaries first, to size the staging buffers once
+    std::vector<size_t> cuts{0};
+    uint64_t need_in = 16, need_cnt = 1;
+    while (first < n) {
+        size_t last = first + 1;
+        while (last < n && last - first < max_sponges && offsets[last + 1] - offsets[first] <= max_el) last++;
+        need_in = std::max<uint64_t>(need_in, (offsets[last] - offsets[first]) * 32);
+        need_cnt = std::max<uint64_t>(need_cnt, last - first);
+        cuts.push_back(last);
+        first = last;
+    }
+    // stage_in: [inputs][offsets (cnt + 1) u64]; stage_out: outputs
+    const size_t in_bytes = (size_t)((need_in + 255) / 256 * 256 + (need_cnt + 1) * 8);
+    st = ensure_staging(ctx, in_bytes, std::max<size_t>((size_t)need_cnt * n_squeeze * 32, 16));
+    if (st != PSD_OK) return st;
+    for (size_t c = 0; c + 1 < cuts.size(); c++, slot = (slot + 1) % kStageSlots) {
+        const size_t lo = cuts[c], hi = cuts[c + 1], cnt = hi - lo;
+        const uint64_t el = offsets[hi] - offsets[lo];
+        cudaStream_t s = ctx->streams[slot];
+        char* d_in = static_cast<char*>(ctx->stage_in[slot]);
+        uint64_t* d_off = reinterpret_cast<uint64_t*>(d_in + (el * 32 + 255) / 256 * 256);
+        if (el) PSD_CUDA(cudaMemcpyAsync(d_in, inputs + offsets[lo] * 4, el * 32, cudaMemcpyHostToDevice, s));
+        PSD_CUDA(cudaMemcpyAsync(d_off, offsets + lo, (cnt + 1) * 8, cudaMemcpyHostToDevice, s));
+        SpongeArgs a = base_args(ctx, cnt);
+        fill(a, reinterpret_cast<const uint32_t*>(d_in), d_off, offsets[lo], static_cast<uint32_t*>(ctx->stage_out[slot]));
+        st = launch(ctx, a, s);
+        if (st != PSD_OK) return st;
+        if (n_squeeze)
+            PSD_CUDA(cudaMemcpyAsync(outputs + lo * n_squeeze * 4, ctx->stage_out[slot], cnt * (size_t)n_squeeze * 32,
+                                     cudaMemcpyDeviceToHost, s));
+    }
+    for (int s = 0; s < kStageSlots; s++) PSD_CUDA(cudaStreamSynchronize(ctx->streams[s]));
+    return check_err_flag(ctx, ctx->streams[0]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// One process, several GPUs.  Sponges never interact (a sponge is a plain value the caller spreads
+// over workers, reference src/poseidon/mod.rs:44-60), so a batch shards into contiguous ranges, one per
+// device, with no exchange at all; the Merkle tree has one exchange step: the subtree roots (32 bytes
+// per device) are copied to the first device's own memory, where the top levels are hashed.
+// ------------------------------------------------------------------------------------------------
+#include <thread>
+
+namespace {
+
+constexpr int kMaxMultiGpus = 64;
+
+// ctxs must be n_gpus distinct contexts of the same parameter set (same numbers; any device each).
+psd_status check_multi(psd_ctx* const* ctxs, int n_gpus) {
+    if (!ctxs) return fail(PSD_ERR_ARG, "null context array");
+    if (n_gpus < 1 || n_gpus > kMaxMultiGpus) return fail(PSD_ERR_ARG, "n_gpus must be in [1, %d]", kMaxMultiGpus);
+    for (int g = 0; g < n_gpus; g++) {
+        if (!ctxs[g]) return fail(PSD_ERR_ARG, "null context at index %d", g);
+        for (int h = 0; h < g; h++)
+            if (ctxs[h] == ctxs[g]) return fail(PSD_ERR_ARG, "context %d and %d are the same object", h, g);
+        const psd_ctx *a = ctxs[0], *b = ctxs[g];
+        if (a->field != b->field || a->t != b->t || a->rate != b->rate || a->full_rounds != b->full_rounds ||
+            a->partial_rounds != b->partial_rounds || a->alpha != b->alpha ||
+            memcmp(a->ark_mont.data(), b->ark_mont.data(), a->ark_mont.size() * sizeof(Fe)) != 0 ||
+            memcmp(a->mds_mont.data(), b->mds_mont.data(), a->mds_mont.size() * sizeof(Fe)) != 0)
+            return fail(PSD_ERR_ARG, "context %d holds a different parameter set than context 0", g);
+    }
+    return PSD_OK;
+}
+
+// Runs work(g) for every device on its own host thread (each drives its own device's streams) and
+// returns the first failure with its message.
+template <class Work>
+psd_status run_per_device(int n_gpus, Work work) {
+    std::vector<psd_status> st((size_t)n_gpus, PSD_OK);
+    std::vector<std::string> msg((size_t)n_gpus);
+    auto body = [&](int g) {
+        st[(size_t)g] = work(g);
+        if (st[(size_t)g] != PSD_OK) msg[(size_t)g] = t_last_error;   // thread-local: copy it out
+    };
+    std::vector<std::thread> threads;
+    for (int g = 1; g < n_gpus; g++) threads.emplace_back(body, g);
+    body(0);
+    for (auto& th : threads) th.join();
+    for (int g = 0; g < n_gpus; g++)
+        if (st[(size_t)g] != PSD_OK) return fail(st[(size_t)g], "device %d of %d: %s", g, n_gpus, msg[(size_t)g].c_str());
+    return PSD_OK;
+}
+
+// Contiguous shard of rank g: the first n % world ranks get one extra unit.
+void shard_range(size_t n, int g, int world, size_t* lo, size_t* hi) {
+    const size_t base = n / (size_t)world, extra = n % (size_t)world;
+    *lo = (size_t)g * base + std::min<size_t>((size_t)g, extra);
+    *hi = *lo + base + ((size_t)g < extra ? 1 : 0);
+}
+
+psd_status staged_shard(psd_ctx* ctx, const uint64_t* inputs, size_t n, uint32_t n_absorb, uint32_t n_squeeze,
+                        uint64_t* outputs, bool permute, int layout, int repr, size_t lo, size_t hi) {
+    if (hi <= lo) return PSD_OK;
+    DeviceGuard guard(ctx->device);
+    if (!guard.ok) return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", ctx->device);
+    if (permute) {
+        auto fill = [&](SpongeArgs& a, void* d_in, void*) {
+            a.state_in = (const uint32_t*)d_in;
+            a.state_in_layout = layout;
+            a.state_in_repr = repr;
+            a.state_out = (uint32_t*)d_in;
+            a.state_out_layout = layout;
+            a.state_out_repr = repr;
+            a.n_raw = 1;
+        };
+        StagedCall c{n, inputs, ctx->t, outputs, ctx->t, 0, layout, true};
+        c.first0 = lo, c.count = hi - lo;
+        return run_staged(ctx, c, fill);
+    }
+    auto fill = [&](SpongeArgs& a, void* d_in, void* d_out) {
+        a.in = (const uint32_t*)d_in;
+        a.n_absorb = n_absorb;
+        a.in_layout = layout;
+        a.in_repr = repr;
+        a.do_squeeze = 1;
+        a.n_squeeze = n_squeeze;
+        a.out = (uint32_t*)d_out;
+        a.out_layout = layout;
+        a.out_repr = repr;
+    };
+    StagedCall c{n, inputs, n_absorb, outputs, n_squeeze, 0, layout, false};
+    c.first0 = lo, c.count = hi - lo;
+    return run_staged(ctx, c, fill);
+}
+
+}  // namespace
+
+extern "C" {
+
+void psd_shard_range(size_t n, int rank, int world, size_t* lo, size_t* hi) {
+    size_t a = 0, b = 0;
+    if (world >= 1 && rank >= 0 && rank < world) shard_range(n, rank, world, &a, &b);
+    if (lo) *lo = a;
+    if (hi) *hi = b;
+}
+
+psd_status psd_permute_batch_multi(psd_ctx* const* ctxs, int n_gpus, uint64_t* states, size_t n, int layout, int repr) {
+    psd_status st = check_multi(ctxs, n_gpus);
+    if (st != PSD_OK) return st;
+    st = check_batch_args(ctxs[0], n ? (void*)states : (void*)ctxs, layout, repr, PSD_MEM_HOST);
+    if (st != PSD_OK || n == 0) return st;
+    return run_per_device(n_gpus, [&](int g) {
+        size_t lo, hi;
+        shard_range(n, g, n_gpus, &lo, &hi);
+        return staged_shard(ctxs[g], states, n, 0, 0, states, true, layout, repr, lo, hi);
+    });
+}
+
+psd_status psd_absorb_squeeze_batch_multi(psd_ctx* const* ctxs, int n_gpus, const uint64_t* inputs, size_t n,
+                                          uint32_t n_absorb, uint32_t n_squeeze, uint64_t* outputs, int layout, int repr) {
+    psd_status st = check_multi(ctxs, n_gpus);
+    if (st != PSD_OK) return st;
+    st = check_batch_args(ctxs[0], (n && n_absorb) ? (const void*)inputs : (const void*)ctxs, layout, repr, PSD_MEM_HOST);
+    if (st != PSD_OK) return st;
+    if (n && n_squeeze && !outputs) return fail(PSD_ERR_ARG, "null output buffer");
+    if (n == 0) return PSD_OK;
+    return run_per_device(n_gpus, [&](int g) {
+        size_t lo, hi;
+        shard_range(n, g, n_gpus, &lo, &hi);
+        return staged_shard(ctxs[g], inputs, n, n_absorb, n_squeeze, outputs, false, layout, repr, lo, hi);
+    });
+}
+
+psd_status psd_merkle_root_multi(psd_ctx* const* ctxs, int n_gpus, const uint64_t* const* leaves_per_gpu,
+                                 size_t leaves_per_gpu_n, uint64_t* root, int repr, int mem, void* const* streams) {
+    psd_status st = check_multi(ctxs, n_gpus);
+    if (st != PSD_OK) return st;
+    if (!leaves_per_gpu || !root) return fail(PSD_ERR_ARG, "null argument");
+    if (!valid_enum(repr, 1) || !valid_enum(mem, 1)) return fail(PSD_ERR_ARG, "bad repr/mem value");
+    for (int g = 0; g < n_gpus; g++)
+        if (!leaves_per_gpu[g]) return fail(PSD_ERR_ARG, "null leaf pointer for device %d", g);
+    if (ctxs[0]->rate < 2) return fail(PSD_ERR_UNSUPPORTED, "2-to-1 compression needs rate >= 2");
+    const size_t L = leaves_per_gpu_n;
+    if (L == 0 || (L & (L - 1))) return fail(PSD_ERR_ARG, "leaves per device must be a power of two");
+    if (n_gpus & (n_gpus - 1)) return fail(PSD_ERR_ARG, "n_gpus must be a power of two");
+    if (n_gpus == 1) return psd_merkle_root(ctxs[0], leaves_per_gpu[0], L, root, repr, mem, streams ? streams[0] : nullptr);
+
+    psd_ctx* c0 = ctxs[0];
+    // every context's Merkle buffers are held for the whole call
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (int g = 0; g < n_gpus; g++) locks.emplace_back(ctxs[g]->merkle_mu);
+    // device 0: room for the gathered subtree roots + the final root, and one event per device
+    {
+        DeviceGuard guard(c0->device);
+        if (!guard.ok) return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", c0->device);
+        if (!c0->multi_roots) PSD_CUDA(cudaMalloc(&c0->multi_roots, (size_t)(kMaxMultiGpus + 1) * 32));
+    }
+    uint32_t* gathered = static_cast<uint32_t*>(c0->multi_roots);          // [n_gpus] elements, device 0
+    uint32_t* d_final = gathered + (size_t)kMaxMultiGpus * 8;               // the root, device 0
+    auto stream_of = [&](int g) {
+        return (mem == PSD_MEM_DEVICE && streams) ? (cudaStream_t)streams[g] : ctxs[g]->streams[0];
+    };
+    // Stage 1, every device on its own thread and stream: [upload] -> subtree levels -> the subtree root
+    // is copied into device 0's buffer (a plain peer copy; no kernel reads another GPU's memory) -> event.
+    // With one leaf per device there is no subtree: the leaves themselves are gathered, in `repr`.
+    const int gathered_repr = L == 1 ? repr : kReprMontgomery;
+    st = run_per_device(n_gpus, [&](int g) -> psd_status {
+        psd_ctx* ctx = ctxs[g];
+        DeviceGuard guard(ctx->device);
+        if (!guard.ok) return fail(PSD_ERR_CUDA, "cudaSetDevice(%d) failed", ctx->device);
+        cudaStream_t s = stream_of(g);
+        if (!ctx->multi_event) PSD_CUDA(cudaEventCreateWithFlags(&ctx->multi_event, cudaEventDisableTiming));
+        if (ctx->device != c0->device) {
+            // direct DMA for the 32-byte copy where the devices can reach each other (NVLink); without it the
+            // runtime stages the copy through the host, which is only slower.  Once per device pair.
+            static std::atomic<uint64_t> tried[64];
+            const uint64_t bit = 1ull << c0->device;
+            if (!(tried[ctx->device].fetch_or(bit) & bit)) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, ctx->device, c0->device) == cudaSuccess && can)
+                    cudaDeviceEnablePeerAccess(c0->device, 0);
+                cudaGetLastError();   // "already enabled" is fine
+            }
+        }
+        const uint32_t* src = as_u32(leaves_per_gpu[g]);
+        if (mem == PSD_MEM_HOST) {
+            psd_status r = merkle_upload_leaves(ctx, leaves_per_gpu[g], L, s, &src);
+            if (r != PSD_OK) return r;
+        }
+        const uint32_t* sub = src;
+        if (L > 1) {
+            psd_status r = merkle_reduce_async(ctx, src, repr, L, nullptr, kReprMontgomery, s, &sub);
+            if (r != PSD_OK) return r;
+        }
+        PSD_CUDA(cudaMemcpyPeerAsync(gathered + (size_t)g * 8, c0->device, sub, ctx->device, 32, s));
+        PSD_CUDA(cudaEventRecord(ctx->multi_event, s));
+        return PSD_OK;
+    });
+    // Stage 2, device 0: wait for every gather, hash the n_gpus local roots, deliver.
+    psd_status result = st;
+    DeviceGuard guard(c0->device);
+    cudaStream_t s0 = stream_of(0);
+    do {
+        if (result != PSD_OK) break;
+        for (int g = 1; g < n_gpus; g++) {
+            if (cudaStreamWaitEvent(s0, ctxs[g]->multi_event, 0) != cudaSuccess) {
+                result = fail(PSD_ERR_CUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString(cudaGetLastError()));
+                break;
+            }
+        }
+        if (result != PSD_OK) break;
+        // the top tree uses the upper part of device 0's scratch as a fresh context would: its own levels fit
+        // in (n_gpus/2 + n_gpus/4) elements, far below what the subtree stage already allocated; but the
+        // subtree stage of device 0 is complete in stream order before this runs, so reuse is safe
+        uint32_t* dst = mem == PSD_MEM_DEVICE ? as_u32(root) : d_final;
+        result = merkle_reduce_async(c0, gathered, gathered_repr, (size_t)n_gpus, dst, repr, s0, nullptr);
+        if (result != PSD_OK) break;
+        if (mem == PSD_MEM_HOST && cudaMemcpyAsync(root, d_final, 32, cudaMemcpyDeviceToHost, s0) != cudaSuccess) {
+            result = fail(PSD_ERR_CUDA, "root download failed: %s", cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+        if (cudaStreamSynchronize(s0) != cudaSuccess) {
+            result = fail(PSD_ERR_CUDA, "top levels failed: %s", cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+    } while (0);
+    // all streams idle before the buffers are released; collect the non-canonical flags of every device
+    for (int g = 0; g < n_gpus; g++) {
+        DeviceGuard dg(ctxs[g]->device);
+        cudaStreamSynchronize(stream_of(g));
+        if (result == PSD_OK && repr == PSD_REPR_CANONICAL) result = check_err_flag(ctxs[g], stream_of(g));
+    }
+    return result;
+}
+
+}  // extern "C"

@@ -39,6 +39,10 @@ struct SpongeArgs {
     uint8_t* out_bytes;
     uint32_t n_bytes;
     int32_t* err;           // device flag: set to 1 if a canonical input was >= p
+    // ragged kernels only: sponge i absorbs elements [in_offsets[i], in_offsets[i+1]) - in_offset_base of `in`
+    // (AoS); n_absorb is ignored
+    const uint64_t* in_offsets;
+    uint64_t in_offset_base;
     // kernels of the shared-memory form only: the context's constant image in global memory (16-byte
     // aligned, pool_words a multiple of 4); d's offsets are relative to it
     const uint32_t* pool_img;

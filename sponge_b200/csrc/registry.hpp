@@ -18,6 +18,7 @@ struct SpongeKernelEntry {
     uint64_t alpha;     // 0 = any alpha (runtime ladder)
     int variant;        // 0 = dense ... 5 = FP64-pipe linear layer (see psd_ctx_set_variant)
     int pool;           // 0 = constants in the unit's constant-bank pool, 1 = staged into shared memory
+    int ragged;         // 1 = per-sponge absorb lengths (SpongeArgs::in_offsets)
     SpongeKernelFn fn;
     const char* name;
 };

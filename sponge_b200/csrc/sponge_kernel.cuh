@@ -97,7 +97,14 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // POOL is part of the kernel's name only so that the constant-bank and the shared-memory build of the same
 // (field, T, ALPHA, VARIANT) are different symbols; the code difference comes from how c_pool is declared
 // in the translation unit (poseidon_core.cuh).
-template <class F, int T, int ALPHA, int VARIANT, int POOL = PSD_POOL_KIND>
+//
+// RAGGED: every sponge absorbs its own number of elements (a.in_offsets), as the reference's callers do when
+// they absorb lists of differing lengths into different sponges (src/poseidon/tests.rs:45-69,
+// absorb.rs:82-101).  The sequencer's variables are per thread already; with differing lengths the threads of
+// a warp simply leave the absorb loop at different times (threads that need no permutation in an iteration
+// idle through it).  A separate instantiation, because inside divergent control flow ptxas keeps the round
+// constants out of the uniform datapath -- the lock-step kernels must not pay for that.
+template <class F, int T, int ALPHA, int VARIANT, int POOL = PSD_POOL_KIND, bool RAGGED = false>
 __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constant__ SpongeArgs a) {
     static_assert(POOL == PSD_POOL_KIND, "POOL must match the translation unit's pool kind");
     const PermDesc& d = a.d;
@@ -143,7 +150,14 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         int mode = a.mode;
         uint32_t idx = a.index;
         uint32_t rem_raw = a.n_raw;
-        uint32_t rem_in = a.n_absorb, k_in = 0;
+        uint32_t n_abs = a.n_absorb;
+        const uint32_t* in_base = a.in;
+        if (RAGGED) {
+            const uint64_t lo = a.in_offsets[i], hi = a.in_offsets[i + 1];
+            n_abs = (uint32_t)(hi - lo);
+            in_base = a.in + (lo - a.in_offset_base) * 8;
+        }
+        uint32_t rem_in = n_abs, k_in = 0;
         uint32_t rem_out = a.n_squeeze, k_out = 0;
         for (;;) {
             bool perm = false;
@@ -158,7 +172,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                     }
                     break;
                 case 1:   // CryptographicSponge::absorb entry, mod.rs:232-254
-                    if (a.n_absorb == 0) {
+                    if (n_abs == 0) {
                         stage = 3;
                         break;
                     }
@@ -220,7 +234,8 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                     const uint32_t j = (uint32_t)l - lane0;
                     if ((uint32_t)l >= lane0 && j < add_cnt) {
                         uint32_t e[8];
-                        load_elem(e, a.in, a.in_layout, a.n, i, a.n_absorb, k_in + j);
+                        if (RAGGED) load_elem(e, in_base, kLayoutAos, 1, 0, 0, k_in + j);
+                        else load_elem(e, a.in, a.in_layout, a.n, i, a.n_absorb, k_in + j);
                         if (a.in_repr == kReprCanonical) {
                             bad |= !is_canonical<F>(e);
                             to_mont<F>(e, d);

@@ -37,8 +37,12 @@ static ConstPoolRegistrar g_pool(TuField::kFieldId, kFp52PoolKey, tu_upload);
 
 #define PSD_REG_FP52(T, ALPHA)                                                                 \
     static SpongeKernelRegistrar g_reg_##T##_##ALPHA(SpongeKernelEntry{                        \
-        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, sponge_kernel<TuField, T, ALPHA, 5>,    \
-        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ">"});
+        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 0, sponge_kernel<TuField, T, ALPHA, 5>, \
+        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ">"}); \
+    static SpongeKernelRegistrar g_regr_##T##_##ALPHA(SpongeKernelEntry{                       \
+        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 1,                                      \
+        sponge_kernel<TuField, T, ALPHA, 5, PSD_POOL_KIND, true>,                              \
+        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ",ragged>"});
 
 PSD_REG_FP52(3, 5)
 PSD_REG_FP52(3, 17)

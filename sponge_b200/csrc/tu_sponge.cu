@@ -35,13 +35,29 @@ static ConstPoolRegistrar g_pool(TuField::kFieldId, PSD_TU_T, tu_upload);
 
 #define PSD_REG(ALPHA, VARIANT)                                                                       \
     static SpongeKernelRegistrar g_reg_##ALPHA##_##VARIANT(SpongeKernelEntry{                         \
-        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND,                                   \
+        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 0,                                \
         sponge_kernel<TuField, PSD_TU_T, ALPHA, VARIANT>,                                             \
         "sponge_kernel<" PSD_TU_FNAME ",t=" PSD_STR(PSD_TU_T) ",alpha=" #ALPHA ",variant=" #VARIANT PSD_POOL_TAG ">"});
+// the same kernel with per-sponge absorb lengths (ragged batches): registered for the forms a context ends
+// up running by default, so that a ragged call never changes the algorithm
+#define PSD_REG_RAGGED(ALPHA, VARIANT)                                                                \
+    static SpongeKernelRegistrar g_regr_##ALPHA##_##VARIANT(SpongeKernelEntry{                        \
+        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 1,                                \
+        sponge_kernel<TuField, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, true>,                        \
+        "sponge_kernel<" PSD_TU_FNAME ",t=" PSD_STR(PSD_TU_T) ",alpha=" #ALPHA ",variant=" #VARIANT PSD_POOL_TAG ",ragged>"});
 
 PSD_REG(0, 0)
+PSD_REG_RAGGED(0, 0)
 #if PSD_TU_T <= 5
 PSD_REG(0, 1)
+PSD_REG_RAGGED(0, 1)
+#endif
+#if PSD_TU_T == 3
+PSD_REG_RAGGED(5, 3)
+PSD_REG_RAGGED(17, 3)
+#endif
+#if PSD_TU_T == 5
+PSD_REG_RAGGED(5, 4)
 #endif
 #if PSD_POOL_KIND == 0
 #if PSD_TU_T == 3 || PSD_TU_T == 5

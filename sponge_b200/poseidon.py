@@ -233,6 +233,17 @@ class PoseidonContext:
                                            L.MEM_HOST, None))
         return out
 
+    def absorb_squeeze_ragged_batch(self, inputs: np.ndarray, offsets: np.ndarray, n_squeeze: int,
+                                    repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
+        """Sponge i absorbs inputs[offsets[i]:offsets[i+1]] (elements) and squeezes n_squeeze elements."""
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = offsets.size - 1
+        assert inputs.dtype == np.uint64 and inputs.flags.c_contiguous and inputs.size == int(offsets[-1]) * 4
+        out = np.zeros((n, n_squeeze, 4), dtype=np.uint64)
+        check(lib.psd_absorb_squeeze_ragged_batch(self.handle, _ptr(inputs) if inputs.size else None, _ptr(offsets), n,
+                                                  n_squeeze, _ptr(out), repr, L.MEM_HOST, None))
+        return out
+
     def absorb_squeeze_bytes_batch(self, inputs: np.ndarray, n: int, n_absorb: int, n_bytes: int,
                                    layout: int = L.LAYOUT_AOS, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
         assert inputs.dtype == np.uint64 and inputs.flags.c_contiguous and inputs.size == n * n_absorb * 4
@@ -309,6 +320,67 @@ class PoseidonContext:
 
 def kernel_launch_count() -> int:
     return int(lib.psd_kernel_launch_count())
+
+
+def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous shard [lo, hi) of `rank` (psd_shard_range): the first n % world ranks get one extra unit."""
+    if not 0 <= rank < world:
+        raise ValueError("rank outside [0, world)")
+    lo, hi = C.c_size_t(), C.c_size_t()
+    lib.psd_shard_range(n, rank, world, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
+class MultiContext:
+    """One parameter set resident on several GPUs of this process (psd_*_multi entry points): host batches
+    are sharded contiguously over the devices with no exchange between them; the Merkle root gathers only
+    the per-device subtree roots."""
+
+    def __init__(self, cfg: PoseidonConfig, devices: Sequence[int]):
+        if len(devices) == 0:
+            raise ValueError("no devices")
+        self.cfg, self.devices = cfg, list(devices)
+        self.ctxs = [PoseidonContext(cfg, d) for d in self.devices]
+        self.t = self.ctxs[0].t
+        self._arr = (C.c_void_p * len(self.ctxs))(*[c.handle for c in self.ctxs])
+
+    def close(self) -> None:
+        for c in self.ctxs:
+            c.close()
+
+    def __len__(self) -> int:
+        return len(self.ctxs)
+
+    def permute_batch(self, states: np.ndarray, layout: int = L.LAYOUT_AOS, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
+        assert states.dtype == np.uint64 and states.flags.c_contiguous and states.size % (4 * self.t) == 0
+        n = states.size // (4 * self.t)
+        check(lib.psd_permute_batch_multi(self._arr, len(self.ctxs), _ptr(states), n, layout, repr))
+        return states
+
+    def absorb_squeeze_batch(self, inputs: np.ndarray, n: int, n_absorb: int, n_squeeze: int,
+                             layout: int = L.LAYOUT_AOS, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
+        assert inputs.dtype == np.uint64 and inputs.flags.c_contiguous and inputs.size == n * n_absorb * 4
+        shape = (n, n_squeeze, 4) if layout == L.LAYOUT_AOS else (n_squeeze, 2, n, 2)
+        out = np.zeros(shape, dtype=np.uint64)
+        check(lib.psd_absorb_squeeze_batch_multi(self._arr, len(self.ctxs), _ptr(inputs), n, n_absorb, n_squeeze,
+                                                 _ptr(out), layout, repr))
+        return out
+
+    def merkle_root(self, leaves: np.ndarray, repr: int = L.REPR_MONTGOMERY) -> np.ndarray:
+        """Root over one contiguous host array of leaves; device g hashes the g-th n/len(devices) slice."""
+        assert leaves.dtype == np.uint64 and leaves.flags.c_contiguous and leaves.size % (4 * len(self.ctxs)) == 0
+        per = leaves.size // 4 // len(self.ctxs)
+        ptrs = (C.c_void_p * len(self.ctxs))(*[leaves.ctypes.data + g * per * 32 for g in range(len(self.ctxs))])
+        root = np.zeros(4, dtype=np.uint64)
+        check(lib.psd_merkle_root_multi(self._arr, len(self.ctxs), ptrs, per, _ptr(root), repr, L.MEM_HOST, None))
+        return root
+
+    def merkle_root_dev(self, leaf_ptrs: Sequence[int], leaves_per_gpu: int, root_ptr: int,
+                        repr: int = L.REPR_MONTGOMERY, streams: Optional[Sequence[int]] = None) -> None:
+        """Device-resident form: leaf_ptrs[g] on device g, root_ptr on the first device."""
+        ptrs = (C.c_void_p * len(self.ctxs))(*leaf_ptrs)
+        st = None if streams is None else (C.c_void_p * len(self.ctxs))(*[s or None for s in streams])
+        check(lib.psd_merkle_root_multi(self._arr, len(self.ctxs), ptrs, leaves_per_gpu, root_ptr, repr, L.MEM_DEVICE, st))
 
 
 class SpongeBatch:

@@ -241,3 +241,57 @@ extern "C" void emu_f52_unpack_pack(const uint32_t* x, uint64_t* limbs, uint32_t
     }
 }
 
+
+// ---- the numeric bounds behind variant 5, evaluated on the product's own image (optionally damaged) --------
+// corrupt: 0 = as built; 1 = one table limb set to 2^52; 2 = every table limb 2^52 - 1 ("all ones": entries
+// >= p); 3 = wrong modulus limb; 4 = every lane-update entry replaced by p - 1 (still residues: must pass);
+// 5 = one additive constant's limb pushed past 2^52.  Returns 1 if the bounds hold, 0 if not, -1 if the
+// variant does not apply to the parameter set; `why` receives the first failed bound.
+extern "C" int emu_fp52_bounds(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, const uint64_t* ark_canon,
+                               const uint64_t* mds_canon, int corrupt, char* why, size_t why_len) {
+    const HostField* hf = host_field(field);
+    const uint32_t t = rate + capacity, rounds = rf + rp;
+    std::vector<Fe> ark(rounds * t), mds(t * t);
+    for (size_t i = 0; i < ark.size(); i++) ark[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(ark_canon)[i]);
+    for (size_t i = 0; i < mds.size(); i++) mds[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(mds_canon)[i]);
+    std::vector<uint32_t> img;
+    PermDesc d{};
+    append_fp52_tables(*hf, t, rf, rp, ark, mds, d, img);
+    if (!d.fp_ok) return -1;
+    auto set_dbl = [&img](uint32_t off8, double x) {
+        uint64_t q;
+        memcpy(&q, &x, 8);
+        img[2 * off8] = (uint32_t)q;
+        img[2 * off8 + 1] = (uint32_t)(q >> 32);
+    };
+    const uint32_t n = t - 1;
+    if (corrupt == 1) set_dbl(d.fp_mat_off + 7, 4503599627370496.0);
+    if (corrupt == 2)
+        for (uint32_t o = d.fp_mat_off; o < d.fp_mat_off + t * t * 25; o++) set_dbl(o, 4503599627370495.0);
+    if (corrupt == 3) set_dbl(d.fp_consts_off + 2, 12345.0);
+    if (corrupt == 4 && rp) {
+        uint64_t pm1[4];
+        const uint64_t one[4] = {1, 0, 0, 0};
+        hf_sub_raw(pm1, hf->p, one);
+        for (uint32_t i = 0; i < rp; i++)
+            for (uint32_t j = 0; j < n; j++)
+                for (int e = 0; e < 5; e++)
+                    for (int l = 0; l < 5; l++) {
+                        const int bit = 52 * l, w = bit / 64, sh = bit % 64;
+                        uint64_t v = pm1[w] >> sh;
+                        if (sh > 12 && w + 1 < 4) v |= pm1[w + 1] << (64 - sh);
+                        set_dbl(d.fp_part_off + (i * 2 * n + n + j) * 25 + e * 5 + l, (double)(v & ((1ull << 52) - 1)));
+                    }
+    }
+    if (corrupt == 5) {
+        const uint32_t o = d.fp_k_off + 2;
+        uint64_t q = (uint64_t)img[2 * o] | ((uint64_t)img[2 * o + 1] << 32);
+        q += 1ull << 52;
+        img[2 * o] = (uint32_t)q;
+        img[2 * o + 1] = (uint32_t)(q >> 32);
+    }
+    std::string reason;
+    const bool ok = fp52_image_bounds_ok(*hf, t, rf, rp, d, img, &reason);
+    if (why && why_len) snprintf(why, why_len, "%s", reason.c_str());
+    return ok ? 1 : 0;
+}

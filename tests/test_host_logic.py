@@ -346,3 +346,27 @@ def test_fp52_primitives_host_model(emu):
     for v, row in zip(vals, lm):
         assert all(r < (1 << 52) for r in row[:4]) and sum(r << (52 * k) for k, r in enumerate(row)) == v
 
+
+
+@pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bn254_t2", "bn254_rp2_alpha17", "bn254_rp1", "bn254_full_only"])
+def test_fp52_bounds_are_evaluated_on_the_tables(emu, ref, name):
+    """Variant 5 is exact only under numeric bounds (table limbs < 2^52, entries < p, rows < p + 2^207, lazily reduced
+    lanes < 2^258, no column wrap, lazy S-box range).  The library evaluates them on the image it is about to upload
+    (fp52_image_bounds_ok, called from append_fp52_tables; a failing image leaves fp_ok = 0 and the context runs an
+    integer variant).  Here: the real tables pass; damaged ones -- a limb of 2^52, an all-ones table, a wrong modulus
+    limb, an additive constant past 2^52 -- are refused with the bound named; lane-update tables replaced by the
+    largest residue p - 1 still pass (the bounds hold for ANY residues)."""
+    cfg = oracle_cfg(ref, name)
+    ark = to_limbs(v for r in cfg.ark for v in r)
+    mds = to_limbs(v for r in cfg.mds for v in r)
+    why = C.create_string_buffer(200)
+
+    def run(corrupt):
+        rc = emu.emu_fp52_bounds(0, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_void_p(ark.ctypes.data),
+                                 C.c_void_p(mds.ctypes.data), corrupt, why, C.c_size_t(200))
+        return rc, why.value.decode()
+    assert run(0) == (1, "")
+    assert run(4)[0] == 1
+    for corrupt, word in ((1, "MDS tables"), (2, "MDS tables"), (3, "modulus"), (5, "additive constant")):
+        rc, msg = run(corrupt)
+        assert rc == 0 and word in msg, (corrupt, rc, msg)
