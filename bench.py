@@ -67,7 +67,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--log-n", type=int, default=None, help="override log2(units per GPU)")
-    ap.add_argument("--variant", type=int, default=5,
+    ap.add_argument("--variant", type=int, default=6,
                     help="0 = dense kernel, 1 = optimised unrolled, 2 = optimised compact, "
                          "3 = compact + digit-table constant products, 5 = integer S-box + FP64-pipe linear "
                          "layer (library default; BN254 t<=3, otherwise runs as 3)")
@@ -252,12 +252,12 @@ def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
     import re
     info = ctx.describe()
     out = dict(kernel=info["kernel_name"], constants_home=info["constants_home"])
-    m = re.match(r"sponge_kernel<(\w+),t=(\d+),alpha=(\d+),variant=(\d+)(,smem)?>", info["kernel_name"])
+    m = re.match(r"sponge_kernel<(\w+),t=(\d+),alpha=(\d+),variant=(\d+)(,smem)?(,ragged)?>", info["kernel_name"])
     if not m:
         return out, None
     fld = "Bn254Fr" if m.group(1) == "bn254" else "Bls12381Fr"
     key = (f"void psd::sponge_kernel<psd::{fld}, (int){m.group(2)}, (int){m.group(3)}, (int){m.group(4)}, "
-           f"(int){1 if m.group(5) else 0}>(psd::SpongeArgs)")
+           f"(int){1 if m.group(5) else 0}, (bool){1 if m.group(6) else 0}>(psd::SpongeArgs)")
     sass = {}
     try:
         sass = json.load(open(os.path.join(ROOT, "sponge_b200", "lib", "kernel_sass.json")))

@@ -18,6 +18,7 @@
 #include "../../include/poseidon_b200.h"
 #include "kernels.cuh"
 #include "fp52_tables.hpp"
+#include "tc_tables.hpp"
 #include "opt_constants.hpp"
 #include "params.hpp"
 #include "registry.hpp"
@@ -110,7 +111,10 @@ static std::atomic<uint64_t> g_launches{0};
 // distinct parameter sets; when it is full the next set goes to the smem home instead of being refused.
 // The small-kernel unit keeps [R, R^2] of both fields at fixed offsets, uploaded once per device.
 // ------------------------------------------------------------------------------------------------
-enum : int { kPoolBank = 0, kPoolSmem = 1 };
+enum : int { kPoolBank = 0, kPoolSmem = 1, kPoolGlobal = 2 };   // kPoolGlobal: read in place (variant-6 tables)
+// pool keys beyond the state widths 2..9
+constexpr int kTcSmallKey = kFp52PoolKey + 1;   // variant 6: the few integer-side constants (staged to shared memory)
+constexpr int kTcTabKey = kFp52PoolKey + 2;     // variant 6: the table image in global memory
 
 struct Placement {
     int device = 0, field = 0, key = 0;
@@ -128,7 +132,7 @@ struct DevicePool {
     std::vector<PoolSlot> used;    // sorted by off
     std::vector<Placement*> live;
 };
-static DevicePool g_pools[64][2][kFp52PoolKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool
+static DevicePool g_pools[64][2][kTcTabKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool; then variant 6's two
 static std::once_flag g_misc_once[64];
 static inline uint32_t misc_one_off(int field) { return (uint32_t)field * 16; }
 static inline uint32_t misc_r2_off(int field) { return (uint32_t)field * 16 + 8; }
@@ -159,12 +163,13 @@ static void slot_free(DevicePool& p, uint32_t off) {
 // try_smem).  The upload is complete when this returns.  nullptr: neither home was possible; *cerr holds
 // the CUDA error if one occurred.
 static Placement* placement_acquire(int device, int field, int key, const std::vector<uint32_t>& words, bool try_bank,
-                                    bool try_smem, cudaError_t* cerr) {
+                                    bool try_smem, cudaError_t* cerr, bool global = false) {
     *cerr = cudaSuccess;
     DevicePool& p = g_pools[device][field][key];
     std::lock_guard<std::mutex> lk(p.mu);
     for (Placement* q : p.live) {
-        if (q->words == words && ((q->kind == kPoolBank && try_bank) || (q->kind == kPoolSmem && try_smem))) {
+        if (q->words == words && ((q->kind == kPoolBank && try_bank) || (q->kind == kPoolSmem && try_smem) ||
+                                  (q->kind == kPoolGlobal && global))) {
             q->refs++;
             return q;
         }
@@ -184,7 +189,7 @@ static Placement* placement_acquire(int device, int field, int key, const std::v
         p.live.push_back(q);
         return q;
     }
-    if (try_smem && words.size() <= kSmemPoolMaxWords) {
+    if ((try_smem && words.size() <= kSmemPoolMaxWords) || global) {
         uint32_t* d = nullptr;
         cudaError_t e = cudaMalloc(&d, words.size() * 4);
         if (e == cudaSuccess) e = cudaMemcpy(d, words.data(), words.size() * 4, cudaMemcpyHostToDevice);
@@ -195,7 +200,8 @@ static Placement* placement_acquire(int device, int field, int key, const std::v
             return nullptr;
         }
         Placement* q = new Placement();
-        q->device = device, q->field = field, q->key = key, q->kind = kPoolSmem, q->d_img = d, q->words = words, q->refs = 1;
+        q->device = device, q->field = field, q->key = key, q->kind = global ? kPoolGlobal : kPoolSmem, q->d_img = d,
+        q->words = words, q->refs = 1;
         p.live.push_back(q);
         return q;
     }
@@ -242,7 +248,13 @@ struct psd_ctx {
     // variant 5 (tu_fp52.cu) has its own image and descriptor; fdesc.fp_ok == 0 when the context has none
     PermDesc fdesc{};
     Placement* pl_fp = nullptr;
-    int variant = 5;   // degrades to 3 / 2 / 0 by what the context has constants for (resolve_kernel)
+    // variant 6 (tu_tc.cu): a small image of the integer-side constants (staged to shared memory) with its
+    // descriptor, and the tensor-core table image in global memory; tcd.ok == 0 when the context has none
+    PermDesc tdesc{};
+    TcDesc tcd{};
+    Placement* pl_tc = nullptr;
+    Placement* pl_tctab = nullptr;
+    int variant = 6;   // degrades to 5 / 3 / 2 / 0 by what the context has constants and kernels for (resolve_kernel)
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;
@@ -339,7 +351,7 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
         // Shared-memory form: every block copies the constant image first, so blocks are as large as the
         // kernel's launch bounds allow once the batch fills the SMs, and shrink (in warps) for small batches
         // so that every SM still gets one.
-        const uint64_t max_block = k->variant == 5 ? 512 : 448;
+        const uint64_t max_block = k->variant >= 5 ? 512 : 448;
         const uint64_t per_sm = (n + sms - 1) / sms;
         cfg.block = (int)std::min<uint64_t>(max_block, std::max<uint64_t>(32, (per_sm + 31) / 32 * 32));
     } else if (k->variant == 5) {
@@ -374,6 +386,15 @@ struct Resolved {
 };
 Resolved resolve_kernel(const psd_ctx* ctx, int ragged = 0) {
     Resolved r;
+    // variant 6 uses warp-collective instructions, so it serves the lock-step calls only; ragged batches take
+    // the next variant down
+    if (ctx->variant >= 6 && !ragged && ctx->pl_tc && ctx->pl_tctab && ctx->tcd.ok) {
+        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 6, kPoolSmem, nullptr, 0);
+        if (k && k->variant == 6) {
+            r.k = k, r.pl = ctx->pl_tc, r.d = &ctx->tdesc;
+            return r;
+        }
+    }
     if (ctx->variant >= 5 && ctx->pl_fp && ctx->fdesc.fp_ok) {
         const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 5, ctx->pl_fp->kind, &ctx->fdesc, ragged);
         if (k && k->variant == 5) {
@@ -405,6 +426,12 @@ psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
         b.pool_img = r.pl->d_img;
         b.pool_words = (uint32_t)r.pl->words.size();
         smem = (size_t)b.pool_words * 4;
+        if (k->variant == 6) {
+            // + the per-warp scratch tiles behind the staged image
+            b.tc = ctx->tcd;
+            b.tc_tab = reinterpret_cast<const unsigned char*>(ctx->pl_tctab->d_img);
+            smem = ((smem + 127) & ~(size_t)127) + (size_t)(cfg.block / 32) * kTcWarpScratch;
+        }
         const int ki = kernel_index(k);
         const uint64_t bit = 1ull << ctx->device;
         if (ki >= 0 && ki < 512 && !(g_smem_attr_done[ki].load(std::memory_order_acquire) & bit)) {
@@ -861,6 +888,47 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
         }
     }
 
+    // Variant 6 (tensor-core linear layer): byte-digit tables in global memory + [ark of round 0][one][r2] staged
+    // to shared memory, for the parameter sets tu_tc.cu has kernels for.
+    {
+        const SpongeKernelEntry* tk = find_kernel(p->field, (int)t, p->alpha, 6, kPoolSmem);
+        if (tk && tk->variant == 6 && tk->alpha == p->alpha && env_int("PSD_NO_TC", 0) == 0) {
+            TcDesc td{};
+            std::vector<uint8_t> tab;
+            build_tc_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, td, tab);
+            if (td.ok) {
+                std::vector<uint32_t> small;
+                auto push_fe3 = [&small](const Fe& f) {
+                    for (int k = 0; k < 4; k++) {
+                        small.push_back((uint32_t)f.v[k]);
+                        small.push_back((uint32_t)(f.v[k] >> 32));
+                    }
+                };
+                PermDesc sd = base_desc;
+                sd.opt_ok = sd.ctab_ok = sd.fp_ok = 0;
+                sd.ark_off = 0;
+                for (uint32_t j = 0; j < t; j++) push_fe3(ctx->ark_mont[j]);
+                sd.mds_off = 0;   // never read by variant 6
+                sd.one_off = (uint32_t)small.size();
+                push_fe3(hf_one(*hf));
+                sd.r2_off = (uint32_t)small.size();
+                push_fe3(r2);
+                std::vector<uint32_t> tabw(tab.size() / 4);
+                memcpy(tabw.data(), tab.data(), tab.size());
+                cudaError_t cerr = cudaSuccess;
+                ctx->pl_tc = placement_acquire(device, p->field, kTcSmallKey, small, false, true, &cerr);
+                if (ctx->pl_tc) ctx->pl_tctab = placement_acquire(device, p->field, kTcTabKey, tabw, false, false, &cerr, true);
+                if (ctx->pl_tc && ctx->pl_tctab) {
+                    ctx->tdesc = sd;
+                    ctx->tcd = td;
+                } else if (cerr != cudaSuccess) {
+                    psd_ctx_destroy(ctx);
+                    return fail(PSD_ERR_CUDA, "uploading the variant-6 tables failed: %s", cudaGetErrorString(cerr));
+                }
+            }
+        }
+    }
+
     auto cleanup = [&](psd_status s) {
         psd_ctx_destroy(ctx);
         return s;
@@ -936,6 +1004,8 @@ static void ctx_teardown(psd_ctx* ctx) {
         if (ctx->multi_event) cudaEventDestroy(ctx->multi_event);
         placement_release(ctx->pl_int);
         placement_release(ctx->pl_fp);
+        placement_release(ctx->pl_tc);
+        placement_release(ctx->pl_tctab);
     }
     delete ctx;
 }
@@ -956,7 +1026,7 @@ psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
 
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
     if (!ctx) return fail(PSD_ERR_ARG, "null context");
-    if (variant < 0 || variant > 5) return fail(PSD_ERR_ARG, "variant must be 0..5");
+    if (variant < 0 || variant > 6) return fail(PSD_ERR_ARG, "variant must be 0..6");
     ctx->variant = variant;
     return PSD_OK;
 }

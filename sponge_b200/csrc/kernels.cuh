@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include "poseidon_core.cuh"
+#include "poseidon_tc.cuh"
 
 namespace psd {
 
@@ -47,6 +48,9 @@ struct SpongeArgs {
     // aligned, pool_words a multiple of 4); d's offsets are relative to it
     const uint32_t* pool_img;
     uint32_t pool_words;
+    // variant 6 only: the tensor-core table image in global memory and where its parts are
+    const unsigned char* tc_tab;
+    TcDesc tc;
 };
 
 struct LaunchCfg {

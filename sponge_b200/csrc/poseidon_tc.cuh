@@ -1,0 +1,283 @@
+// VARIANT 6: the optimised Poseidon permutation with the S-box on the integer multiplier and the whole linear
+// layer on the TENSOR CORES.  Same function, bit for bit, as poseidon/mod.rs:95-118.
+//
+// A t x t MDS product over 254-bit integers is not a contraction -- but a product by a ROUND CONSTANT is, once
+// the constant is expanded into a digit table: for a constant c the host stores the 32 x 32 byte matrix
+//     Tab_c[k][col] = byte `col` of ( c * 256^k * 2^32 mod p ),        k, col = 0..31
+// and then, for any 256-bit x with bytes x_k,
+//     x * c * 2^32  ==  sum_col 256^col * ( sum_k x_k * Tab_c[k][col] )      (mod p).
+// Over the 32 sponges of a warp the inner sums are an integer GEMM  [32 sponges x 32 T bytes] x [32 T x 32]  with
+// u8 operands and s32 accumulation (column sums < 32 T 255^2 < 2^24 for T <= 5): mma.sync.m16n8k32.u8.u8.s32,
+// two m-tiles per warp, A fragments built from the thread-per-sponge registers through shared memory + ldmatrix,
+// B fragments (the tables, pre-arranged by the host in fragment order) read from global memory / L1 with one
+// 64-bit load per pair of MMAs.  What remains per output value is a "sweep" by the thread that owns the sponge:
+// the 32 byte-weighted column sums come back through shared memory, are folded into nine 32-bit limbs (value
+// < 2^272.1) and ONE 32-bit Montgomery row divides the 2^32 back out: result < p + 2^241, congruent to the exact
+// field value -- a valid input for the lazy S-box (fp256.cuh) and for the next round's byte expansion.
+// Additive round constants enter as the initial values of the accumulators (bytes of K * 2^32 mod p).
+//
+// Round structure: the regrouped (sparse) form of opt_constants.cpp, as in variants 1-5.  In the partial
+// rounds lane j >= 1 is updated as  s_j' = 1 * s_j + v_j * y  with BOTH terms through the tensor cores (the
+// identity's table costs one more k-step and returns a value that is bounded again, so lanes never grow), and
+// lives only as A fragments between rounds.
+//
+// Nothing here touches the FP64 pipe and the integer multiplier sees only the S-box and 8 multiplies per
+// sweep: per partial round (t = 3) 352 + 24 IMAD.WIDE against 730 in variant 3, and about 900 instructions
+// against 1 528 in variant 5.
+#pragma once
+#include "poseidon_core.cuh"
+
+namespace psd {
+
+constexpr uint32_t kTcFragBytes = 1024;   // one constant: 4 n-tiles x 32 lanes x (b0, b1)
+constexpr uint32_t kTcKBytes = 128;       // one additive constant: 4 n-tiles x 4 column pairs x 2 x s32
+// per-warp shared-memory scratch: two A tiles (32 sponges x 32 bytes, rows padded to 48) and two column-sum
+// exchange tiles (32 sponges x 16 words, rows padded to 20 words); consecutive uses alternate between the two
+// copies so that only the write -> read direction needs a warp barrier
+constexpr uint32_t kTcARow = 48, kTcATile = 32 * kTcARow;
+constexpr uint32_t kTcCRow = 80, kTcCTile = 32 * kTcCRow;
+constexpr uint32_t kTcWarpScratch = 2 * kTcATile + 2 * kTcCTile;   // 8 192 bytes
+
+// Where variant 6 finds its tables (byte offsets into the global image `tab`), see tc_tables.cpp.
+struct TcDesc {
+    uint32_t ok;
+    uint32_t mat_off;     // [T][T] fragments of the dense matrix ([0][0] doubles as M00)
+    uint32_t pre_off;     // [T][T] fragments of M_pre
+    uint32_t ident_off;   // fragment of the constant 1
+    uint32_t part_off;    // [partial][2(T-1)] fragments: w_1.., v_1.. per partial round
+    uint32_t k_off;       // [rounds][T] additive constants (accumulator start values), execution order
+};
+
+// the lazy S-box of fp256.cuh / poseidon_core.cuh on a value < p + 2^241 (BN254), else the reducing one after one
+// conditional subtraction
+template <class F, int ALPHA>
+PSD_DEV void tc_sbox(uint32_t* x) {
+    constexpr bool kLazy = (F::kBits == 254);
+    uint32_t in[8];
+    if (kLazy) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) in[k] = x[k];
+    } else {
+        cond_sub_p<F>(in, x);
+    }
+    uint32_t y[8];
+    fp_sqr<F, !kLazy>(y, in);
+#pragma unroll
+    for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, !kLazy>(y, y);
+    mont_mul<F, !kLazy>(x, y, in);
+}
+
+#if defined(__CUDACC__)
+
+struct TcWarp {
+    unsigned char* scratch;   // this warp's kTcWarpScratch bytes of shared memory
+    const unsigned char* tab; // the context's table image in global memory
+    int lane;
+    uint32_t a_use, c_use;    // which copy of the A / C tile the next use takes
+};
+
+__device__ __forceinline__ void tc_mma(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// x (8 words = 32 little-endian bytes of this thread's sponge) -> A fragments of the warp's two 16-sponge m-tiles
+__device__ __forceinline__ void tc_pack(uint32_t (&a)[2][4], const uint32_t* x, TcWarp& w) {
+    unsigned char* tile = w.scratch + (w.a_use & 1) * kTcATile;
+    w.a_use++;
+    uint4* row = reinterpret_cast<uint4*>(tile + w.lane * kTcARow);
+    row[0] = make_uint4(x[0], x[1], x[2], x[3]);
+    row[1] = make_uint4(x[4], x[5], x[6], x[7]);
+    __syncwarp();
+    // ldmatrix.x4: lane L supplies the address of row (L & 7) of 8x8 b16 matrix (L >> 3); matrix q covers sponges
+    // 8 (q & 1) .. + 7 of the m-tile and bytes 16 (q >> 1) .. + 15, which is the a0..a3 order of m16n8k32
+    const int q = w.lane >> 3, r = w.lane & 7;
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++) {
+        const unsigned char* src = tile + (mt * 16 + (q & 1) * 8 + r) * kTcARow + (q >> 1) * 16;
+        const uint32_t addr = (uint32_t)__cvta_generic_to_shared(src);
+        asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(a[mt][0]), "=r"(a[mt][1]), "=r"(a[mt][2]), "=r"(a[mt][3])
+                     : "r"(addr)
+                     : "memory");
+    }
+}
+
+// accumulators <- the additive constant's bytes (columns 8 nt + 2 tg, + 1 of every row this thread holds)
+__device__ __forceinline__ void tc_init(int (&acc)[2][4][4], const unsigned char* kfrag, const TcWarp& w) {
+    const int tg = w.lane & 3;
+#pragma unroll
+    for (int nt = 0; nt < 4; nt++) {
+        const int2 v = __ldg(reinterpret_cast<const int2*>(kfrag) + nt * 4 + tg);
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            acc[mt][nt][0] = v.x;
+            acc[mt][nt][1] = v.y;
+            acc[mt][nt][2] = v.x;
+            acc[mt][nt][3] = v.y;
+        }
+    }
+}
+
+// accumulators += bytes(value behind the A fragments) x Tab_c, c given by its fragment block
+__device__ __forceinline__ void tc_mac(int (&acc)[2][4][4], const uint32_t (&a)[2][4], const unsigned char* frag, const TcWarp& w) {
+#pragma unroll
+    for (int nt = 0; nt < 4; nt++) {
+        const uint2 b = __ldg(reinterpret_cast<const uint2*>(frag) + nt * 32 + w.lane);
+        tc_mma(acc[0][nt], a[0], b.x, b.y);
+        tc_mma(acc[1][nt], a[1], b.x, b.y);
+    }
+}
+
+// column sums of one output value -> 8 x 32-bit limbs of THIS thread's sponge, value < p + 2^241:
+// pair-combine, exchange through shared memory, carry sweep, one 32-bit Montgomery row
+template <class F>
+__device__ __forceinline__ void tc_sweep(uint32_t* out, const int (&acc)[2][4][4], TcWarp& w) {
+    unsigned char* tile = w.scratch + 2 * kTcATile + (w.c_use & 1) * kTcCTile;
+    w.c_use++;
+    const int g = w.lane >> 2, tg = w.lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            // sponge g + 8 h + 16 mt, columns 8 nt + 2 tg and + 1:  P = c_even + 256 c_odd  (< 2^32: sums < 2^32 / 257)
+            uint32_t P[4];
+#pragma unroll
+            for (int nt = 0; nt < 4; nt++) P[nt] = (uint32_t)acc[mt][nt][2 * h] + ((uint32_t)acc[mt][nt][2 * h + 1] << 8);
+            *reinterpret_cast<uint4*>(tile + (g + 8 * h + 16 * mt) * kTcCRow + tg * 16) = make_uint4(P[0], P[1], P[2], P[3]);
+        }
+    __syncwarp();
+    uint32_t Q[4][4];   // [column pair tg][n-tile] of this thread's sponge
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint4 v = *reinterpret_cast<const uint4*>(tile + w.lane * kTcCRow + k * 16);
+        Q[k][0] = v.x; Q[k][1] = v.y; Q[k][2] = v.z; Q[k][3] = v.w;
+    }
+    // value = sum_{nt, k} Q[k][nt] 2^(64 nt + 16 k)  ->  v[0..8]
+    uint32_t v[9];
+    uint64_t carry = 0;
+#pragma unroll
+    for (int nt = 0; nt < 4; nt++) {
+        const uint64_t lo = (uint64_t)Q[0][nt] + ((uint64_t)Q[1][nt] << 16) + carry;          // < 2^50
+        const uint64_t hi = (uint64_t)Q[2][nt] + ((uint64_t)Q[3][nt] << 16) + (lo >> 32);     // < 2^50
+        v[2 * nt] = (uint32_t)lo;
+        v[2 * nt + 1] = (uint32_t)hi;
+        carry = hi >> 32;
+    }
+    v[8] = (uint32_t)carry;
+    // Montgomery row: (V + m p) / 2^32, m = -V / p mod 2^32.  First the even limbs of p onto columns 0..7 (column 0
+    // becomes zero), then the odd limbs onto columns 1..8; the carry out of column 8 is provably zero
+    // (V + m p < 2^273 + 2^286 < 2^288).
+    const uint32_t m = v[0] * np0<F>();
+    uint32_t c8 = 0;
+    mad4(v, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, c8);
+    uint32_t x[8] = {v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8] + c8};
+    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+#pragma unroll
+    for (int k = 0; k < 8; k++) out[k] = x[k];
+}
+
+// One full round on limb states: T S-boxes, then T rows of `mat` (each: constant start values, T k-steps, sweep).
+// Free functions rather than lambdas: a lambda's call operator is not force-inlined, and an outlined round
+// would pass its arrays through local memory.
+template <class F, int T, int ALPHA>
+__device__ __forceinline__ void tc_full_round(uint32_t (&st)[T][8], const unsigned char* mat, const unsigned char* kp, TcWarp& w) {
+    uint32_t aX[T][2][4];
+#pragma unroll
+    for (int j = 0; j < T; j++) {
+        tc_sbox<F, ALPHA>(st[j]);
+        tc_pack(aX[j], st[j], w);
+    }
+    int acc[2][4][4];
+#pragma unroll
+    for (int i = 0; i < T; i++) {
+        tc_init(acc, kp + i * kTcKBytes, w);
+#pragma unroll
+        for (int j = 0; j < T; j++) tc_mac(acc, aX[j], mat + (i * T + j) * kTcFragBytes, w);
+        tc_sweep<F>(st[i], acc, w);
+    }
+}
+
+// One partial round.  Lanes 1..T-1 live as A fragments (aL) between partial rounds; LAST: the updated lanes are
+// needed as limbs again (full rounds follow), so they are not re-packed.
+template <class F, int T, int ALPHA, bool LAST>
+__device__ __forceinline__ void tc_partial_round(uint32_t (&st)[T][8], uint32_t (&aL)[T - 1][2][4], const unsigned char* m00,
+                                                 const unsigned char* ident, const unsigned char* part, const unsigned char* kp,
+                                                 TcWarp& w) {
+    uint32_t aY[2][4];
+    tc_sbox<F, ALPHA>(st[0]);
+    tc_pack(aY, st[0], w);
+    int acc[2][4][4];
+    // row 0: M00 y + sum_j w_j s_j + k
+    tc_init(acc, kp, w);
+    tc_mac(acc, aY, m00, w);
+#pragma unroll
+    for (int j = 1; j < T; j++) tc_mac(acc, aL[j - 1], part + (j - 1) * kTcFragBytes, w);
+    tc_sweep<F>(st[0], acc, w);
+    // lanes: s_j' = 1 s_j + v_j y (+ the leftover constant after the last partial round)
+#pragma unroll
+    for (int j = 1; j < T; j++) {
+        tc_init(acc, kp + j * kTcKBytes, w);
+        tc_mac(acc, aY, part + (T - 1 + j - 1) * kTcFragBytes, w);
+        tc_mac(acc, aL[j - 1], ident, w);
+        tc_sweep<F>(st[j], acc, w);
+        if (!LAST) tc_pack(aL[j - 1], st[j], w);
+    }
+}
+
+template <class F, int T, int ALPHA>
+__device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, TcWarp& w) {
+    static_assert(ALPHA == 5 || ALPHA == 17, "variant 6: alpha 5 or 17");
+    // round-0 constants on the integer side
+#pragma unroll
+    for (int j = 0; j < T; j++) {
+        uint32_t c[8];
+        cload8(c, d.ark_off + j * 8);
+        fp_add<F>(st[j], st[j], c);
+    }
+    const uint32_t half = d.half_full, rp = d.partial;
+    const unsigned char* kp = w.tab + td.k_off;
+
+#pragma unroll 1
+    for (uint32_t r = 0; r < half; r++) {
+        tc_full_round<F, T, ALPHA>(st, w.tab + ((r + 1 == half && rp) ? td.pre_off : td.mat_off), kp, w);
+        kp += T * kTcKBytes;
+    }
+
+    if (rp) {
+        uint32_t aL[T - 1][2][4];
+#pragma unroll
+        for (int j = 1; j < T; j++) tc_pack(aL[j - 1], st[j], w);
+        const unsigned char* part = w.tab + td.part_off;
+        const unsigned char* m00 = w.tab + td.mat_off;
+        const unsigned char* ident = w.tab + td.ident_off;
+#pragma unroll 1
+        for (uint32_t i = 0; i + 1 < rp; i++) {
+            tc_partial_round<F, T, ALPHA, false>(st, aL, m00, ident, part, kp, w);
+            kp += T * kTcKBytes;
+            part += 2 * (T - 1) * kTcFragBytes;
+        }
+        tc_partial_round<F, T, ALPHA, true>(st, aL, m00, ident, part, kp, w);
+        kp += T * kTcKBytes;
+    }
+
+#pragma unroll 1
+    for (uint32_t r = half + rp; r < d.total; r++) {
+        tc_full_round<F, T, ALPHA>(st, w.tab + td.mat_off, kp, w);
+        kp += T * kTcKBytes;
+    }
+
+    // sweeps leave values < p + 2^241: one conditional subtraction gives the canonical residue
+#pragma unroll
+    for (int j = 0; j < T; j++) {
+        uint32_t x[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) x[k] = st[j][k];
+        cond_sub_p<F>(st[j], x);
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace psd

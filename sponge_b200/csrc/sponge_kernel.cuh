@@ -49,6 +49,7 @@ __device__ __forceinline__ void store_elem(const uint32_t* x, uint32_t* base, in
 // ------------------------------------------------------------------------------------------------
 template <class F, int T, int ALPHA, int VARIANT>
 __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d) {
+    static_assert(VARIANT != 6, "variant 6 is called with its warp context (permute_tc)");
     if constexpr (VARIANT == 5) {
         permute_fp52<F, T, ALPHA>(st, d);       // the host only selects this kernel when d.fp_ok
     } else if constexpr (T > 5) {
@@ -85,8 +86,8 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // Shared-memory form (POOL == 1): every block carries its own copy of the constant image, so blocks are
 // large -- variant 5 as above (512 threads, one block per SM), the integer variants 448 threads with two
 // blocks per SM (the 28 warps per SM that seven 128-thread blocks give the constant-bank form).
-#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 5 ? 512 : 448)
-#define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) == 5 ? 1 : 2)
+#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) >= 5 ? 512 : 448)
+#define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) >= 5 ? 1 : 2)
 #if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
 #define PSD_POOL_KIND 1
 #define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_SMEM_BLOCK(VARIANT), PSD_SMEM_BLOCKS(VARIANT))
@@ -125,8 +126,23 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
     // (potentially divergent) per-thread loop ptxas stops using the uniform datapath, and every
     // round-constant read turns from LDCU + uniform-register operand into LEA + LDC into a vector
     // register (measured: +6 % instructions on the compact kernel, +10 % on the digit-table one).
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.n) return;
+    // Variant 6 runs warp-collective instructions (mma.sync, ldmatrix) inside the permutation, so the threads of
+    // the last, partly filled warp stay alive: they recompute the last sponge and store nothing.
+    const uint64_t i_raw = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i_raw < a.n;
+    if (VARIANT != 6 && !live) return;
+    const uint64_t i = live ? i_raw : a.n - 1;
+#if PSD_POOL_KIND == 1
+    TcWarp tcw;
+    if (VARIANT == 6) {
+        // per-warp scratch behind the staged constant image (128-byte aligned)
+        unsigned char* base = reinterpret_cast<unsigned char*>(c_pool) + ((a.pool_words * 4u + 127u) & ~127u);
+        tcw.scratch = base + (threadIdx.x >> 5) * kTcWarpScratch;
+        tcw.tab = a.tc_tab;
+        tcw.lane = threadIdx.x & 31;
+        tcw.a_use = tcw.c_use = 0;
+    }
+#endif
     {
         uint32_t st[T][8];
         if (a.state_in != nullptr) {
@@ -254,7 +270,9 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                         uint32_t e[8];
 #pragma unroll
                         for (int k = 0; k < 8; k++) e[k] = st[l][k];
-                        if (a.out_bytes != nullptr) {
+                        if (VARIANT == 6 && !live) {
+                            // a padding thread of the last warp: nothing to deliver
+                        } else if (a.out_bytes != nullptr) {
                             // squeeze_bytes, mod.rs:256-270: first 31 LE bytes of the canonical value
                             from_mont<F>(e);
                             const uint32_t usable = (F::kBits - 1) / 8;
@@ -272,13 +290,17 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                 rem_out -= emit_cnt;
             }
             if (perm) {
-                permute<F, T, ALPHA, VARIANT>(st, d);
+#if PSD_POOL_KIND == 1
+                if constexpr (VARIANT == 6) permute_tc<F, T, ALPHA>(st, d, a.tc, tcw);
+                else
+#endif
+                    permute<F, T, ALPHA, VARIANT>(st, d);
             } else if (stage == 5) {
                 break;
             }
         }
 
-        if (a.state_out != nullptr) {
+        if (a.state_out != nullptr && (VARIANT != 6 || live)) {
 #pragma unroll
             for (int l = 0; l < T; l++) {
                 uint32_t e[8];
@@ -289,7 +311,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             }
         }
     }
-    if (bad && a.err) atomicOr(a.err, 1);
+    if (bad && a.err && live) atomicOr(a.err, 1);
 }
 
 }  // namespace psd

@@ -1,0 +1,206 @@
+// Host-side (one-time) tables for the tensor-core linear layer (poseidon_tc.cuh).
+//
+// Everything is derived from the regrouped constants of opt_constants.cpp (M_pre, the sparse rows (M00, w), the
+// lane coefficients v, the per-round constants k_i and post_ark), exactly as the FP64-pipe variant does
+// (fp52_tables.cpp).  A constant c (true value; the state holds Montgomery residues, and (xR) c = (xc) R) becomes the
+// 32 x 32 byte matrix Tab_c[k][col] = byte col of (c 256^k 2^32 mod p); the 2^32 is divided out again by the one
+// Montgomery row of the sweep.  An additive constant K (a Montgomery residue) becomes the bytes of K 2^32 mod p,
+// the start values of the accumulators.
+#include "tc_tables.hpp"
+
+#include <string.h>
+
+namespace psd {
+
+namespace {
+
+struct Pow2m {
+    const HostField& f;
+    Fe two;
+    explicit Pow2m(const HostField& hf) : f(hf) {
+        Fe t = {{2, 0, 0, 0}};
+        two = hf_to_mont(f, t);
+    }
+    Fe operator()(uint64_t e) const { return hf_pow_u64(f, two, e); }   // Montgomery form of 2^e mod p
+};
+
+Fe fe_at(const std::vector<uint32_t>& img, uint32_t word_off) {
+    Fe x;
+    for (int k = 0; k < 4; k++) x.v[k] = (uint64_t)img[word_off + 2 * k] | ((uint64_t)img[word_off + 2 * k + 1] << 32);
+    return x;
+}
+
+inline uint8_t byte_of(const Fe& x, int b) { return (uint8_t)(x.v[b / 8] >> (8 * (b % 8))); }
+
+// fragment block of the constant with Montgomery form c_mont: for n-tile nt, lane L = 4 g + tg:
+//   b0 = Tab[4 tg + 0..3][8 nt + g],  b1 = Tab[16 + 4 tg + 0..3][8 nt + g]      (lowest byte first)
+void push_frag(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[32], const Fe& c_mont) {
+    Fe tab[32];   // tab[k] = c 256^k 2^32 mod p, canonical
+    for (int k = 0; k < 32; k++) tab[k] = hf_from_mont(f, hf_mul(f, c_mont, pow_mont[k]));
+    for (int nt = 0; nt < 4; nt++)
+        for (int lane = 0; lane < 32; lane++) {
+            const int g = lane >> 2, tg = lane & 3, col = 8 * nt + g;
+            for (int i = 0; i < 4; i++) img.push_back(byte_of(tab[4 * tg + i], col));
+            for (int i = 0; i < 4; i++) img.push_back(byte_of(tab[16 + 4 * tg + i], col));
+        }
+}
+
+// accumulator start values of the additive constant with Montgomery residue k_mont: bytes of K' = K 2^32 mod p;
+// for n-tile nt and column pair tg two little-endian s32: K'[8 nt + 2 tg], K'[8 nt + 2 tg + 1]
+void push_kfrag(std::vector<uint8_t>& img, const HostField& f, const Fe& pow32_mont, const Fe& k_mont) {
+    // k_mont IS the integer to be added to the state (a residue below p); K' = k_mont * 2^32 mod p as an integer:
+    // hf_mul(a, b) = a b / R, so with b = 2^32 R mod p (the Montgomery form of 2^32) the product is a 2^32 mod p.
+    const Fe kp = hf_mul(f, k_mont, pow32_mont);
+    for (int nt = 0; nt < 4; nt++)
+        for (int tg = 0; tg < 4; tg++)
+            for (int e = 0; e < 2; e++) {
+                const uint32_t v = byte_of(kp, 8 * nt + 2 * tg + e);
+                for (int b = 0; b < 4; b++) img.push_back((uint8_t)(v >> (8 * b)));
+            }
+}
+
+}  // namespace
+
+bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why) {
+    auto no = [&](const char* m) {
+        if (why) *why = m;
+        return false;
+    };
+    if (t < 2 || t > 5) return no("width outside [2,5]");
+    // column sums: 32 t products of two bytes plus one constant byte; pair-combining needs sum * 257 < 2^32
+    const uint64_t colmax = 32ull * t * 255 * 255 + 255;
+    if (colmax * 257 >= (1ull << 32)) return no("column sums too large for the pair-combine");
+    // sweep input V < colmax * 256^32 * 256/255 ; result (V + m p) / 2^32 < V / 2^32 + p must stay below 2^256 and,
+    // for the lazy S-box (BN254), inside its operand range 2 a + p < 2^256 with the output below 2^256
+    long double p = 0;
+    for (int k = 3; k >= 0; k--) p = p * 0x1p64L + (long double)f.p[k];
+    const long double vmax = (long double)colmax * 0x1p256L * (256.0L / 255.0L);
+    const long double res = vmax / 0x1p32L + p;
+    if (res >= 0x1p256L) return no("sweep results do not fit 256 bits");
+    if (f.bits == 254) {
+        const long double q = p / 0x1p256L;
+        long double y = res / p;
+        const long double x0 = y;
+        for (int sq = 0; sq < 4; sq++) {
+            if ((2 * y + 1) * p >= 0x1p256L) return no("a squaring operand leaves the 9-limb window");
+            y = 1 + y * y * q;
+        }
+        if ((y + 1) * p >= 0x1p256L) return no("the closing product's operand is too large");
+        if ((1 + y * x0 * q) * p >= 0x1p256L) return no("the lazy S-box output does not fit 256 bits");
+    } else if (res >= 2 * p) {
+        return no("sweep results are not below 2p");
+    }
+    return true;
+}
+
+void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
+                     const std::vector<Fe>& ark, const std::vector<Fe>& mds, TcDesc& td, std::vector<uint8_t>& img) {
+    memset(&td, 0, sizeof td);
+    img.clear();
+    const uint32_t half = full_rounds / 2, rp = partial_rounds, n = t - 1, total = full_rounds + rp;
+    if (half == 0 || full_rounds - half == 0) return;
+    if (!tc_bounds_ok(f, t, nullptr)) return;
+
+    // the regrouped constants, from a scratch image
+    PermDesc od{};
+    std::vector<uint32_t> oimg;
+    append_optimised_constants(f, t, full_rounds, rp, ark, mds, od, oimg);
+    if (!od.opt_ok) return;
+    std::vector<Fe> m_pre, k_lane0(rp), post_ark(t);
+    std::vector<std::vector<Fe>> w(rp), v(rp);
+    if (rp) {
+        for (uint32_t i = 0; i < t * t; i++) m_pre.push_back(fe_at(oimg, od.pre_mds_off + i * 8));
+        for (uint32_t r = 0; r < rp; r++) {
+            const uint32_t base = od.sparse_off + r * 2 * t * 8;
+            k_lane0[r] = fe_at(oimg, base);
+            for (uint32_t j = 0; j < n; j++) w[r].push_back(fe_at(oimg, base + (2 + j) * 8));
+            for (uint32_t j = 0; j < n; j++) v[r].push_back(fe_at(oimg, base + (2 + n + j) * 8));
+        }
+        for (uint32_t j = 0; j < t; j++) post_ark[j] = fe_at(oimg, od.post_ark_off + j * 8);
+    }
+
+    const Pow2m pow2(f);
+    Fe pow_mont[32];
+    for (int k = 0; k < 32; k++) pow_mont[k] = pow2(8 * k + 32);
+    const Fe pow32 = pow2(32);
+    auto here = [&img]() { return (uint32_t)img.size(); };
+
+    td.mat_off = here();
+    for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, mds[i]);
+    if (rp) {
+        td.pre_off = here();
+        for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, m_pre[i]);
+    }
+    td.ident_off = here();
+    push_frag(img, f, pow_mont, hf_one(f));
+    td.part_off = here();
+    for (uint32_t i = 0; i < rp; i++) {
+        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j]);
+        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j]);
+    }
+    // additive constants in execution order, t per round: what round r's outputs receive is what round r + 1
+    // adds before its S-boxes
+    td.k_off = here();
+    const Fe zero = hf_zero();
+    for (uint32_t r = 0; r < total; r++) {
+        const bool full = r < half || r >= half + rp;
+        const bool last_partial = !full && r + 1 == half + rp;
+        for (uint32_t j = 0; j < t; j++) {
+            Fe k = zero;
+            if (last_partial) k = post_ark[j];
+            else if (!full) k = (j == 0) ? k_lane0[r - half + 1] : zero;
+            else if (r + 1 == half && rp) k = (j == 0) ? k_lane0[0] : zero;
+            else if (r + 1 < total) k = ark[(size_t)(r + 1) * t + j];
+            push_kfrag(img, f, pow32, k);
+        }
+    }
+    while (img.size() % 16) img.push_back(0);
+    td.ok = 1;
+}
+
+void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const uint8_t* const* frags, const uint8_t* kfrag,
+                 uint32_t* out8) {
+    // column sums, read back from the fragment layout
+    uint64_t col[32];
+    for (int c = 0; c < 32; c++) {
+        const int nt = c / 8, tg = (c % 8) / 2, e = c % 2;
+        const uint8_t* q = kfrag + ((nt * 4 + tg) * 2 + e) * 4;
+        col[c] = (uint64_t)q[0] | ((uint64_t)q[1] << 8) | ((uint64_t)q[2] << 16) | ((uint64_t)q[3] << 24);
+    }
+    for (uint32_t j = 0; j < n_terms; j++)
+        for (int k = 0; k < 32; k++) {
+            const uint32_t byte = (x[j * 8 + k / 4] >> (8 * (k % 4))) & 0xff;
+            for (int c = 0; c < 32; c++) {
+                const int nt = c / 8, g = c % 8;
+                const int tg = (k % 16) / 4, i = k % 4, hi = k / 16;
+                const uint8_t tb = frags[j][((nt * 32 + (4 * g + tg)) * 2 + hi) * 4 + i];
+                col[c] += (uint64_t)byte * tb;
+            }
+        }
+    // V = sum col[c] 256^c  (nine 32-bit limbs)
+    uint32_t v[10] = {0};
+    {
+        unsigned __int128 carry = 0;
+        for (int l = 0; l < 9; l++) {
+            unsigned __int128 s = carry;
+            for (int b = 0; b < 4; b++)
+                if (4 * l + b < 32) s += (unsigned __int128)col[4 * l + b] << (8 * b);
+            v[l] = (uint32_t)s;
+            carry = s >> 32;
+        }
+    }
+    // one 32-bit Montgomery row
+    const uint32_t p32[8] = {(uint32_t)f.p[0], (uint32_t)(f.p[0] >> 32), (uint32_t)f.p[1], (uint32_t)(f.p[1] >> 32),
+                             (uint32_t)f.p[2], (uint32_t)(f.p[2] >> 32), (uint32_t)f.p[3], (uint32_t)(f.p[3] >> 32)};
+    const uint32_t m = v[0] * (uint32_t)f.np0;
+    uint64_t c = 0;
+    uint32_t r[10];
+    for (int l = 0; l < 9; l++) {
+        const unsigned __int128 ss = (unsigned __int128)v[l] + (l < 8 ? (unsigned __int128)m * p32[l] : 0) + c;
+        r[l] = (uint32_t)ss;
+        c = (uint64_t)(ss >> 32);
+    }
+    for (int l = 0; l < 8; l++) out8[l] = r[l + 1];
+}
+
+}  // namespace psd

@@ -1,0 +1,28 @@
+// Tables for the tensor-core linear layer (variant 6; host, one-time) -- see tc_tables.cpp / poseidon_tc.cuh.
+#pragma once
+#include <string>
+
+#include "opt_constants.hpp"
+#include "poseidon_tc.cuh"
+
+namespace psd {
+
+// Builds the variant-6 table image for one parameter set (Montgomery inputs): byte-digit tables of every
+// constant that multiplies the state, pre-arranged in mma.m16n8k32 B-fragment order, and the additive
+// constants as accumulator start values.  td.ok is set when the variant applies (a factorable matrix, full
+// rounds on both sides of the partial rounds, width <= 5) and the numeric bounds hold.
+void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
+                     const std::vector<Fe>& ark_mont, const std::vector<Fe>& mds_mont, TcDesc& td,
+                     std::vector<uint8_t>& img);
+
+// The numeric conditions behind variant 6 for a given field and width: column sums below 2^32 / 257, sweep
+// results below 2^256 and inside the S-box's operand range.  *why names the first one that fails.
+bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why);
+
+// Host model of what the device computes for ONE output value (used by tests/emu): the sweep of
+// sum_j bytes(x_j) * Tab(c_j) + K' followed by one 32-bit Montgomery row.  x: n_terms values of 8 words
+// (any 256-bit integers), frags / kfrag as laid out by build_tc_tables.
+void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const uint8_t* const* frags, const uint8_t* kfrag,
+                 uint32_t* out8);
+
+}  // namespace psd

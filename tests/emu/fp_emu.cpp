@@ -295,3 +295,117 @@ extern "C" int emu_fp52_bounds(int field, uint32_t rate, uint32_t capacity, uint
     if (why && why_len) snprintf(why, why_len, "%s", reason.c_str());
     return ok ? 1 : 0;
 }
+
+// ---- host model of VARIANT 6 (tensor-core linear layer): the product's own tables (tc_tables.cpp) driven per sponge
+// by tc_host_row -- the same column sums, sweep and Montgomery row the device computes with mma.sync -- and the
+// device's integer S-box code.  Checks the table construction, the constant ordering and the bounds without a GPU.
+#include "../../sponge_b200/csrc/tc_tables.hpp"
+
+template <class F, int T, int ALPHA>
+static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf) {
+    for (int j = 0; j < T; j++) {
+        uint32_t c[8];
+        cload8(c, d.ark_off + j * 8);
+        fp_add<F>(st[j], st[j], c);
+    }
+    const uint32_t half = d.half_full, rp = d.partial;
+    const uint8_t* kp = tab + td.k_off;
+    auto full_round = [&](const uint8_t* mat) {
+        uint32_t y[T][8];
+        for (int j = 0; j < T; j++) {
+            tc_sbox<F, ALPHA>(st[j]);
+            memcpy(y[j], st[j], 32);
+        }
+        for (int i = 0; i < T; i++) {
+            const uint8_t* frags[T];
+            for (int j = 0; j < T; j++) frags[j] = mat + (i * T + j) * kTcFragBytes;
+            tc_host_row(hf, &y[0][0], T, frags, kp + i * kTcKBytes, st[i]);
+        }
+        kp += T * kTcKBytes;
+    };
+    for (uint32_t r = 0; r < half; r++) full_round(tab + ((r + 1 == half && rp) ? td.pre_off : td.mat_off));
+    if (rp) {
+        const uint8_t* part = tab + td.part_off;
+        for (uint32_t i = 0; i < rp; i++) {
+            tc_sbox<F, ALPHA>(st[0]);
+            uint32_t terms[T][8];
+            const uint8_t* frags[T];
+            memcpy(terms[0], st[0], 32);
+            frags[0] = tab + td.mat_off;
+            for (int j = 1; j < T; j++) {
+                memcpy(terms[j], st[j], 32);
+                frags[j] = part + (j - 1) * kTcFragBytes;
+            }
+            uint32_t n0[8];
+            tc_host_row(hf, &terms[0][0], T, frags, kp, n0);
+            for (int j = 1; j < T; j++) {
+                uint32_t two[2][8];
+                memcpy(two[0], st[0], 32);   // y
+                memcpy(two[1], st[j], 32);   // the lane
+                const uint8_t* fr[2] = {part + (T - 1 + j - 1) * kTcFragBytes, tab + td.ident_off};
+                tc_host_row(hf, &two[0][0], 2, fr, kp + j * kTcKBytes, st[j]);
+            }
+            memcpy(st[0], n0, 32);
+            kp += T * kTcKBytes;
+            part += 2 * (T - 1) * kTcFragBytes;
+        }
+    }
+    for (uint32_t r = half + rp; r < d.total; r++) full_round(tab + td.mat_off);
+    for (int j = 0; j < T; j++) {
+        uint32_t x[8];
+        memcpy(x, st[j], 32);
+        cond_sub_p<F>(st[j], x);
+    }
+}
+
+template <class F, int T>
+static int emu_perm_tc_a(uint64_t alpha, const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf, uint32_t* states,
+                         size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        uint32_t s[T][8];
+        memcpy(s, states + i * T * 8, sizeof s);
+        if (alpha == 5) emu_perm_tc_one<F, T, 5>(s, d, td, tab, hf);
+        else if (alpha == 17) emu_perm_tc_one<F, T, 17>(s, d, td, tab, hf);
+        else return 1;
+        memcpy(states + i * T * 8, s, sizeof s);
+    }
+    return 0;
+}
+
+// returns 0 ok, 1 if variant 6 does not apply to the parameter set, -1 unsupported width
+extern "C" int emu_permute_tc(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, uint64_t alpha,
+                              const uint64_t* ark_canon, const uint64_t* mds_canon, uint32_t* states, size_t n) {
+    const HostField* hf = host_field(field);
+    const uint32_t t = rate + capacity, rounds = rf + rp;
+    std::vector<Fe> ark(rounds * t), mds(t * t);
+    for (size_t i = 0; i < ark.size(); i++) ark[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(ark_canon)[i]);
+    for (size_t i = 0; i < mds.size(); i++) mds[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(mds_canon)[i]);
+    TcDesc td{};
+    std::vector<uint8_t> tab;
+    build_tc_tables(*hf, t, rf, rp, ark, mds, td, tab);
+    if (!td.ok) return 1;
+    PermDesc d{};
+    d.ark_off = 0;
+    for (uint32_t j = 0; j < t; j++)
+        for (int k = 0; k < 4; k++) {
+            c_pool[j * 8 + 2 * k] = (uint32_t)ark[j].v[k];
+            c_pool[j * 8 + 2 * k + 1] = (uint32_t)(ark[j].v[k] >> 32);
+        }
+    d.half_full = rf / 2; d.partial = rp; d.total = rounds; d.rate = rate; d.capacity = capacity;
+    if (field == 0) {
+        switch (t) {
+            case 2: return emu_perm_tc_a<Bn254Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
+            case 3: return emu_perm_tc_a<Bn254Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
+            case 4: return emu_perm_tc_a<Bn254Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+            case 5: return emu_perm_tc_a<Bn254Fr, 5>(alpha, d, td, tab.data(), *hf, states, n);
+        }
+    } else {
+        switch (t) {
+            case 2: return emu_perm_tc_a<Bls12381Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
+            case 3: return emu_perm_tc_a<Bls12381Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
+            case 4: return emu_perm_tc_a<Bls12381Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+            case 5: return emu_perm_tc_a<Bls12381Fr, 5>(alpha, d, td, tab.data(), *hf, states, n);
+        }
+    }
+    return -1;
+}

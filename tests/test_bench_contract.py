@@ -38,3 +38,24 @@ def test_reference_arm_other_ranks_exit_quietly():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                          capture_output=True, text=True, env=env, timeout=120)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_executed_work_block_reads_the_build_time_kernel_facts():
+    """bench.py's roofline.exec block: the kernel a context reports is looked up in the SASS facts written at build
+    time (sponge_b200/lib/kernel_sass.json); no GPU needed for the lookup itself."""
+    sys.path.insert(0, ROOT)
+    import bench
+
+    class FakeCtx:
+        def __init__(self, name):
+            self.name = name
+
+        def describe(self):
+            return dict(kernel_name=self.name, constants_home="bank", variant=5, image_bytes=0, image_shared_by=1)
+
+    for name in ("sponge_kernel<bn254,t=3,alpha=5,variant=5>", "sponge_kernel<bn254,t=3,alpha=5,variant=6,smem>",
+                 "sponge_kernel<bn254,t=5,alpha=5,variant=5,smem>", "sponge_kernel<bls12_381,t=3,alpha=17,variant=3>",
+                 "sponge_kernel<bn254,t=3,alpha=5,variant=5,ragged>"):
+        info, traffic = bench.executed_work(FakeCtx(name), "c2", 24, 1 << 24, 96.0, dict(sm_mhz=1965.0))
+        assert info["kernel"] == name
+        assert "sass_sha256" in info and info["static_instructions"] > 1000, (name, info)

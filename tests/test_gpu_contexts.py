@@ -40,6 +40,10 @@ def test_many_live_parameter_sets(ref, field, rate, rf, rp, alpha):
         for skip in range(4):   # four different MDS matrices -> four different parameter sets, all alive
             ocfg, cfg = make_cfg(S, ref, p, rate, rf, rp, alpha, skip)
             live.append((ocfg, S.PoseidonContext(cfg, 0)))
+        variants = [c.describe()["variant"] for _, c in live]
+        assert len(set(variants)) == 1, f"parameter sets of one shape run different algorithms by default: {variants}"
+        for _, c in live:
+            c.set_variant(5)   # the forms whose constants compete for the constant bank
         homes = [c.describe()["constants_home"] for _, c in live]
         assert homes[0] == "bank" or (field == "bn254" and t == 5), homes   # t=5 variant 5 exists in the shared form only
         if t in (3, 5):
@@ -57,7 +61,7 @@ def test_many_live_parameter_sets(ref, field, rate, rf, rp, alpha):
         orc = COracle(ocfg, field_id(ref, ocfg))
         st = orc.synth(600 * t, seed=0xF1)
         exp = orc.permute_batch(st.copy())
-        for v in (0, 1, 2, 3, 5):
+        for v in (0, 1, 2, 3, 5, 6):
             ctx.set_variant(v)
             assert np.array_equal(ctx.permute_batch(st.copy()), exp), (v, ctx.describe())
     finally:
@@ -72,6 +76,9 @@ def test_identical_parameter_sets_share_one_image(ref):
     b = S.PoseidonContext(cfg, 0)
     c = S.PoseidonContext(cfg, 0)
     try:
+        assert a.describe()["image_shared_by"] == 3          # whatever the default kernel reads is shared too
+        for x in (a, b, c):
+            x.set_variant(5)
         da, dc = a.describe(), c.describe()
         assert dc["image_shared_by"] == 3 and da["constants_home"] == dc["constants_home"] == "bank"
         assert da["kernel_name"] == dc["kernel_name"]
@@ -84,13 +91,15 @@ def test_identical_parameter_sets_share_one_image(ref):
     ocfg2, cfg2 = make_cfg(S, ref, ref.BN254_FR, 2, 8, 57, 5, 1)
     d = S.PoseidonContext(cfg2, 0)
     try:
+        d.set_variant(5)
         assert d.describe()["constants_home"] == "bank"
     finally:
         d.close()
 
 
 def test_second_parameter_set_is_not_a_performance_cliff(ref):
-    """Two live BN254 t=3 parameter sets: both report what they run, both run variant 5, and the one in the
+    """Two live BN254 t=3 parameter sets: both report what they run and get the same default kernel; with variant 5
+    requested (the form whose tables compete for the constant bank) both run variant 5, and the one in the
     shared-memory form is within 10 % of the one in the constant bank on 2^20 permutations."""
     import torch
     import sponge_b200 as S
@@ -98,6 +107,9 @@ def test_second_parameter_set_is_not_a_performance_cliff(ref):
     _, cfg2 = make_cfg(S, ref, ref.BN254_FR, 2, 8, 57, 5, 1)
     c1, c2 = S.PoseidonContext(cfg1, 0), S.PoseidonContext(cfg2, 0)
     try:
+        assert c1.describe()["variant"] == c2.describe()["variant"]   # the default is the same for both
+        c1.set_variant(5)
+        c2.set_variant(5)
         d1, d2 = c1.describe(), c2.describe()
         assert d1["variant"] == d2["variant"] == 5
         assert (d1["constants_home"], d2["constants_home"]) == ("bank", "shared")

@@ -142,10 +142,11 @@ def test_c5_shape_long_absorb_in_chunks(S, ref):
 
 
 @pytest.mark.parametrize("name,absorb", [("bn254_t3", 0), ("bn254_t5", 4)])
-def test_variant5_equals_dense_on_every_element_of_the_full_batch(S, ref, name, absorb):
-    """The shipped default kernel (variant 5: 52-bit limbs on the FP64 pipe, lazily reduced lanes) against the
-    dense reference-order kernel (variant 0, itself oracle-tested) on ALL 2^24 items of C2 / C3, compared on
-    the device -- not a sample: a carry corner that fires once in 2^24 inputs shows up here."""
+def test_fast_variants_equal_dense_on_every_element_of_the_full_batch(S, ref, name, absorb):
+    """The fast kernels (variant 6: tensor-core linear layer; variant 5: 52-bit limbs on the FP64 pipe, lazily
+    reduced lanes) against the dense reference-order kernel (variant 0, itself oracle-tested) on ALL 2^24 items
+    of C2 / C3, compared on the device -- not a sample: a carry corner that fires once in 2^24 inputs shows up
+    here."""
     import torch
     _, orc, ctx = make(S, ref, name)
     try:
@@ -155,7 +156,7 @@ def test_variant5_equals_dense_on_every_element_of_the_full_batch(S, ref, name, 
         x = torch.empty((n * width, 4), dtype=torch.int64, device="cuda:0")
         ctx.synth_fill_dev(x.data_ptr(), n * width, 0x5D0)
         outs = []
-        for variant in (5, 0):
+        for variant in (6, 5, 0):
             ctx.set_variant(variant)
             assert ctx.active_variant() == variant
             if absorb == 0:
@@ -166,8 +167,9 @@ def test_variant5_equals_dense_on_every_element_of_the_full_batch(S, ref, name, 
                 ctx.absorb_squeeze_batch_dev(x.data_ptr(), n, absorb, 1, y.data_ptr())
             ctx.synchronize()
             outs.append(y)
-        assert torch.equal(outs[0], outs[1])
-        # anchor the pair to the oracle on a few items
+        assert torch.equal(outs[0], outs[2])
+        assert torch.equal(outs[1], outs[2])
+        # anchor them to the oracle on a few items
         idx = np.array([0, 1, n // 3, n - 1])
         got = outs[0].view(n, -1)[torch.from_numpy(idx).to("cuda:0")].cpu().numpy().view(np.uint64)
         inp = np.concatenate([orc.synth(width, 0x5D0, first=int(i) * width) for i in idx])

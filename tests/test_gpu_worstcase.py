@@ -1,4 +1,4 @@
-"""Worst-case intermediate states for the shipped default kernel (variant 5).
+"""Worst-case intermediate states for the shipped fast kernels (variants 6 and 5).
 
 Random inputs almost never put an extreme value INSIDE the permutation: the state after the S-box of round r
 is uniformly random whatever the input was.  Here the extreme values are placed there on purpose: a target
@@ -6,7 +6,7 @@ state right after the S-box layer of a chosen round (lane values 0, p-1, 2^253, 
 is p-1 / 2^253 / 2^208-1 / all 52-bit limbs set, ...) is mapped BACK to the permutation's input by running the
 oracle's rounds in reverse -- inverse MDS, minus the round constants, alpha-th root (alpha^-1 mod p-1) -- so
 that the forward run passes through exactly that state.  Rounds: the first and last of both full-round groups
-and the first, second, a middle and the last two partial rounds.  The GPU result (variant 5, and variant 3 as
+and the first, second, a middle and the last two partial rounds.  The GPU result (variants 6 and 5, and variant 3 as
 the all-integer cross-check) must equal the Python oracle's forward permutation bit for bit, and the oracle's
 own forward run is asserted to hit the target, so the construction itself is checked.
 
@@ -101,10 +101,10 @@ def test_extreme_values_inside_the_permutation(ref, name):
                             field_name(ref, cfg))
     ctx = pcfg.context()
     try:
-        for variant in (5, 3, 0):
+        for variant in (6, 5, 3, 0):
             ctx.set_variant(variant)
-            if variant == 5:
-                assert ctx.active_variant() == 5, ctx.describe()
+            if variant >= 5:
+                assert ctx.active_variant() == variant, ctx.describe()
             got = to_ints(ctx.permute_batch(flat_in.copy(), repr=S.REPR_CANONICAL))
             got = [got[i * t:(i + 1) * t] for i in range(len(inputs))]
             bad = [i for i in range(len(inputs)) if got[i] != expected[i]]

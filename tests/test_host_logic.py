@@ -130,11 +130,11 @@ def emu():
     so = os.path.join(ROOT, "tests", "emu", "libfp_emu_san.so" if san else "libfp_emu.so")
     csrc = os.path.join(ROOT, "sponge_b200", "csrc")
     srcs = [os.path.join(ROOT, "tests", "emu", "fp_emu.cpp"), os.path.join(csrc, "opt_constants.cpp"),
-            os.path.join(csrc, "fp52_tables.cpp"),
+            os.path.join(csrc, "fp52_tables.cpp"), os.path.join(csrc, "tc_tables.cpp"),
             os.path.join(csrc, "params.cpp")]
     deps = srcs + [os.path.join(csrc, h) for h in ("fp256.cuh", "poseidon_core.cuh", "opt_constants.hpp",
                                                    "host_field.hpp", "params.hpp", "fp52.cuh", "poseidon_fp52.cuh",
-                                                   "fp52_tables.hpp")]
+                                                   "fp52_tables.hpp", "poseidon_tc.cuh", "tc_tables.hpp")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(d) for d in deps):
         # -frounding-math: fp52.cuh's host model runs fma() under FE_TOWARDZERO
         flags = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=all"] if san else ["-O2"]
@@ -370,3 +370,34 @@ def test_fp52_bounds_are_evaluated_on_the_tables(emu, ref, name):
     for corrupt, word in ((1, "MDS tables"), (2, "MDS tables"), (3, "modulus"), (5, "additive constant")):
         rc, msg = run(corrupt)
         assert rc == 0 and word in msg, (corrupt, rc, msg)
+
+
+@pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bn254_t2", "bn254_t4_cap2", "bn254_rp2_alpha17", "bn254_rp1",
+                                  "bn254_full_only", "bls_fixture", "bls_default_r2", "bls_t3_alpha5", "bn254_odd_rf"])
+def test_tensor_core_variant_host_model(emu, ref, name):
+    """Variant 6 without a GPU: the product's own byte-digit tables (tc_tables.cpp, in mma fragment order) driven per
+    sponge by the host model of one output value -- column sums, carry sweep, one 32-bit Montgomery row -- and the
+    device's integer S-box code, against the oracle.  Checks the table construction, the ordering of the additive
+    constants and the bounds; the fragment plumbing (mma.sync, ldmatrix, shared-memory exchange) is covered by the
+    -m gpu tests."""
+    from conftest import field_id
+    from oracle.c_oracle import COracle
+    cfg = oracle_cfg(ref, name)
+    fid = field_id(ref, cfg)
+    t = cfg.rate + cfg.capacity
+    orc = COracle(cfg, fid)
+    n = 24
+    st = orc.synth(n * t, seed=6)
+    st[:t] = 0
+    st[t:2 * t] = to_limbs([cfg.p - 1] * t)
+    exp = orc.permute_batch(st.copy())
+    ark = to_limbs(v for r in cfg.ark for v in r)
+    mds = to_limbs(v for r in cfg.mds for v in r)
+    s = st.copy().view(np.uint32)
+    rc = emu.emu_permute_tc(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
+                            C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), C.c_void_p(s.ctypes.data), C.c_size_t(n))
+    if cfg.alpha not in (5, 17):
+        assert rc == 1
+        return
+    assert rc == 0
+    assert np.array_equal(s.view(np.uint64), exp)
