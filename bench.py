@@ -587,8 +587,17 @@ def main():
     merkle = None
     if world > 1 and not args.no_merkle:
         barrier()
+        # While rank 0 drives every GPU the other ranks must wait on the HOST: an NCCL barrier would park a spinning
+        # kernel of another process on each GPU, and kernels of different processes time-slice (measured at N = 2: the
+        # tree took twice as long with the other rank inside dist.barrier()).
+        store = dist.distributed_c10d._get_default_store()
         if rank == 0:
-            merkle = multi_gpu_merkle(S, cfg, world, args)
+            try:
+                merkle = multi_gpu_merkle(S, cfg, world, args)
+            finally:
+                store.set("psd_bench_merkle_done", "1")
+        else:
+            store.wait(["psd_bench_merkle_done"])
         barrier()
 
     if rank != 0:

@@ -292,7 +292,12 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 2 = optimised, compact rolled phases,
  * 3 = 2 + products by round constants through digit tables (t = 3; 4 = the t = 5 form: lane updates only),
  * 5 = integer S-box + the whole linear layer on the FP64 pipe in 52-bit limbs (BN254 Fr, t = 2, 3, 5,
- *     alpha 5 or 17) -- the default where it exists.
+ *     alpha 5 or 17),
+ * 6 = integer S-box + the whole linear layer on the tensor cores: every product by a round constant is a
+ *     u8 x u8 -> s32 matrix product against the constant's 32 x 32 byte-digit table (mma.sync.m16n8k32),
+ *     followed by one carry sweep and one 32-bit Montgomery row per output value (t = 2..5, alpha 5 or
+ *     17, both fields).  The default for BN254 Fr; BLS12-381 Fr defaults to 5 -> 3 (variant 6 measured
+ *     slower there).  Lock-step calls only: ragged batches run the next variant down.
  * A request is served by the best kernel <= it that exists for the context's field, width and home of
  * constants; psd_ctx_active_variant / psd_ctx_describe report what a launch really runs.
  *
@@ -303,7 +308,9 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * the bank, then falls back to the shared-memory form, which any number of parameter sets can use at
  * once -- so creating a context never fails for lack of constant-bank space and a second parameter set
  * of the same shape runs the same algorithm as the first (measured within a few percent; the t = 5
- * variant-5 tables, 100 KiB, exist in the shared-memory form only). */
+ * variant-5 tables, 100 KiB, exist in the shared-memory form only).  Variant 6 keeps its tables (1 KiB per
+ * constant, 250 KiB for t = 3) in global memory, where the L1/L2 caches serve them, and stages only the
+ * round-0 constants; any number of parameter sets can use it at once. */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
 psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant);
 typedef enum psd_constants_home { PSD_CONSTANTS_BANK = 0, PSD_CONSTANTS_SHARED = 1 } psd_constants_home;

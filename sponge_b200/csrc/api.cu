@@ -351,7 +351,7 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
         // Shared-memory form: every block copies the constant image first, so blocks are as large as the
         // kernel's launch bounds allow once the batch fills the SMs, and shrink (in warps) for small batches
         // so that every SM still gets one.
-        const uint64_t max_block = k->variant >= 5 ? 512 : 448;
+        const uint64_t max_block = (uint64_t)k->max_block;
         const uint64_t per_sm = (n + sms - 1) / sms;
         cfg.block = (int)std::min<uint64_t>(max_block, std::max<uint64_t>(32, (per_sm + 31) / 32 * 32));
     } else if (k->variant == 5) {
@@ -430,6 +430,8 @@ psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
             // + the per-warp scratch tiles behind the staged image
             b.tc = ctx->tcd;
             b.tc_tab = reinterpret_cast<const unsigned char*>(ctx->pl_tctab->d_img);
+            static const int stagger = env_int("PSD_TC_STAGGER", 1500);   // cycles; measured on c2/c3: +0.5 % / +1.4 % over starting together
+            b.tc_stagger = cfg.block >= 256 ? (uint32_t)std::max(0, stagger) : 0u;
             smem = ((smem + 127) & ~(size_t)127) + (size_t)(cfg.block / 32) * kTcWarpScratch;
         }
         const int ki = kernel_index(k);
@@ -748,6 +750,10 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->capacity = p->capacity;
     ctx->t = t;
     ctx->alpha = p->alpha;
+    // Default request: the tensor-core form for BN254 (c2: 197 M perm/s against 174 M for variant 5); for BLS12-381
+    // (alpha = 17 S-boxes with full reductions dominate) it measured SLOWER than the all-integer variant 3 on c5
+    // (126 M against 169 M perm/s), so that field asks for 5 and gets 3; psd_ctx_set_variant(ctx, 6) still selects it.
+    ctx->variant = p->field == PSD_FIELD_BN254_FR ? 6 : 5;
 
     // constants -> Montgomery
     const Fe* ark = reinterpret_cast<const Fe*>(p->ark);

@@ -51,6 +51,7 @@ struct SpongeArgs {
     // variant 6 only: the tensor-core table image in global memory and where its parts are
     const unsigned char* tc_tab;
     TcDesc tc;
+    uint32_t tc_stagger;    // cycles by which the warps that share a scheduler start apart (0 = together)
 };
 
 struct LaunchCfg {

@@ -27,6 +27,10 @@
 #pragma once
 #include "poseidon_core.cuh"
 
+#ifndef PSD_TC_PIPELINE
+#define PSD_TC_PIPELINE 1
+#endif
+
 namespace psd {
 
 constexpr uint32_t kTcFragBytes = 1024;   // one constant: 4 n-tiles x 32 lanes x (b0, b1)
@@ -199,30 +203,40 @@ __device__ __forceinline__ void tc_full_round(uint32_t (&st)[T][8], const unsign
     }
 }
 
-// One partial round.  Lanes 1..T-1 live as A fragments (aL) between partial rounds; LAST: the updated lanes are
-// needed as limbs again (full rounds follow), so they are not re-packed.
-template <class F, int T, int ALPHA, bool LAST>
-__device__ __forceinline__ void tc_partial_round(uint32_t (&st)[T][8], uint32_t (&aL)[T - 1][2][4], const unsigned char* m00,
-                                                 const unsigned char* ident, const unsigned char* part, const unsigned char* kp,
-                                                 TcWarp& w) {
-    uint32_t aY[2][4];
-    tc_sbox<F, ALPHA>(st[0]);
-    tc_pack(aY, st[0], w);
+// Partial rounds, software-pipelined.  Only lane 0's chain  S-box -> row 0 -> S-box  is serial; the lane updates of
+// round i depend on y_i alone, so they are written NEXT TO the S-box of round i + 1: the S-box keeps the integer
+// multiplier busy while the lane updates use the tensor cores and shared memory.
+//   tc_row0:   st0 <- M00 y + sum_j w_j s_j + k        (y, lanes given as A fragments)
+//   tc_lanes:  s_j <- 1 s_j + v_j y + k_j               (REPACK: result back to A fragments, else to limbs)
+template <class F, int T>
+__device__ __forceinline__ void tc_row0(uint32_t* st0, const uint32_t (&aY)[2][4], const uint32_t (&aL)[T - 1][2][4],
+                                        const unsigned char* m00, const unsigned char* part, const unsigned char* kp, TcWarp& w) {
     int acc[2][4][4];
-    // row 0: M00 y + sum_j w_j s_j + k
     tc_init(acc, kp, w);
     tc_mac(acc, aY, m00, w);
 #pragma unroll
     for (int j = 1; j < T; j++) tc_mac(acc, aL[j - 1], part + (j - 1) * kTcFragBytes, w);
-    tc_sweep<F>(st[0], acc, w);
-    // lanes: s_j' = 1 s_j + v_j y (+ the leftover constant after the last partial round)
+    tc_sweep<F>(st0, acc, w);
+}
+
+template <class F, int T, bool REPACK>
+__device__ __forceinline__ void tc_lanes(uint32_t (&st)[T][8], const uint32_t (&aY)[2][4], uint32_t (&aL)[T - 1][2][4],
+                                         const unsigned char* ident, const unsigned char* part, const unsigned char* kp,
+                                         TcWarp& w) {
 #pragma unroll
     for (int j = 1; j < T; j++) {
+        int acc[2][4][4];
         tc_init(acc, kp + j * kTcKBytes, w);
         tc_mac(acc, aY, part + (T - 1 + j - 1) * kTcFragBytes, w);
         tc_mac(acc, aL[j - 1], ident, w);
-        tc_sweep<F>(st[j], acc, w);
-        if (!LAST) tc_pack(aL[j - 1], st[j], w);
+        uint32_t lane[8];
+        tc_sweep<F>(lane, acc, w);
+        if (REPACK) {
+            tc_pack(aL[j - 1], lane, w);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) st[j][k] = lane[k];
+        }
     }
 }
 
@@ -246,19 +260,38 @@ __device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc&
     }
 
     if (rp) {
-        uint32_t aL[T - 1][2][4];
+        uint32_t aL[T - 1][2][4], aY[2][4];
 #pragma unroll
         for (int j = 1; j < T; j++) tc_pack(aL[j - 1], st[j], w);
         const unsigned char* part = w.tab + td.part_off;
         const unsigned char* m00 = w.tab + td.mat_off;
         const unsigned char* ident = w.tab + td.ident_off;
+        tc_sbox<F, ALPHA>(st[0]);
+        tc_pack(aY, st[0], w);
 #pragma unroll 1
         for (uint32_t i = 0; i + 1 < rp; i++) {
-            tc_partial_round<F, T, ALPHA, false>(st, aL, m00, ident, part, kp, w);
+            tc_row0<F, T>(st[0], aY, aL, m00, part, kp, w);
+            // independent of each other: the S-box of round i + 1 and the lane updates of round i
+            uint32_t aYn[2][4];
+#if PSD_TC_PIPELINE
+            tc_sbox<F, ALPHA>(st[0]);
+            tc_lanes<F, T, true>(st, aY, aL, ident, part, kp, w);
+#else
+            tc_lanes<F, T, true>(st, aY, aL, ident, part, kp, w);
+            __syncwarp();   // keeps the two phases apart in the schedule (fewer live registers, more warps)
+            tc_sbox<F, ALPHA>(st[0]);
+#endif
+            tc_pack(aYn, st[0], w);
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+                for (int q = 0; q < 4; q++) aY[mt][q] = aYn[mt][q];
             kp += T * kTcKBytes;
             part += 2 * (T - 1) * kTcFragBytes;
         }
-        tc_partial_round<F, T, ALPHA, true>(st, aL, m00, ident, part, kp, w);
+        // last partial round: the updated lanes are needed as limbs again (full rounds follow)
+        tc_row0<F, T>(st[0], aY, aL, m00, part, kp, w);
+        tc_lanes<F, T, false>(st, aY, aL, ident, part, kp, w);
         kp += T * kTcKBytes;
     }
 

@@ -19,6 +19,7 @@ struct SpongeKernelEntry {
     int variant;        // 0 = dense ... 5 = FP64-pipe linear layer (see psd_ctx_set_variant)
     int pool;           // 0 = constants in the unit's constant-bank pool, 1 = staged into shared memory
     int ragged;         // 1 = per-sponge absorb lengths (SpongeArgs::in_offsets)
+    int max_block;      // largest block size the kernel was compiled for (its __launch_bounds__)
     SpongeKernelFn fn;
     const char* name;
 };

@@ -86,14 +86,21 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 // Shared-memory form (POOL == 1): every block carries its own copy of the constant image, so blocks are
 // large -- variant 5 as above (512 threads, one block per SM), the integer variants 448 threads with two
 // blocks per SM (the 28 warps per SM that seven 128-thread blocks give the constant-bank form).
-#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) >= 5 ? 512 : 448)
+// Variant 6: block size is a build-time choice (PSD_TC_BLOCK, default 512): larger blocks mean more warps per
+// scheduler to hide the S-box's dependency chains, at fewer registers per thread.
+#ifndef PSD_TC_BLOCK
+#define PSD_TC_BLOCK 512
+#endif
+#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 5 ? 512 : 448)
 #define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) >= 5 ? 1 : 2)
 #if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
 #define PSD_POOL_KIND 1
 #define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_SMEM_BLOCK(VARIANT), PSD_SMEM_BLOCKS(VARIANT))
+#define PSD_MAX_BLOCK(VARIANT) PSD_SMEM_BLOCK(VARIANT)
 #else
 #define PSD_POOL_KIND 0
 #define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_KERNEL_MAX_BLOCK(VARIANT), PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT))
+#define PSD_MAX_BLOCK(VARIANT) PSD_KERNEL_MAX_BLOCK(VARIANT)
 #endif
 // POOL is part of the kernel's name only so that the constant-bank and the shared-memory build of the same
 // (field, T, ALPHA, VARIANT) are different symbols; the code difference comes from how c_pool is declared
@@ -141,6 +148,15 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         tcw.tab = a.tc_tab;
         tcw.lane = threadIdx.x & 31;
         tcw.a_use = tcw.c_use = 0;
+        // The warps of a block start together and would stay in phase: all in the S-box (integer multiplier busy,
+        // tensor cores and shared memory idle), then all in the linear layer (the reverse).  Starting the warps that
+        // share a scheduler (w, w+4, w+8, w+12) a fraction of a round apart lets the two halves overlap.
+        if (a.tc_stagger) {
+            const long long t0 = clock64();
+            const long long wait = (long long)((threadIdx.x >> 7) & 3) * a.tc_stagger;
+            while (clock64() - t0 < wait) {
+            }
+        }
     }
 #endif
     {

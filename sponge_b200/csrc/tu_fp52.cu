@@ -37,10 +37,10 @@ static ConstPoolRegistrar g_pool(TuField::kFieldId, kFp52PoolKey, tu_upload);
 
 #define PSD_REG_FP52(T, ALPHA)                                                                 \
     static SpongeKernelRegistrar g_reg_##T##_##ALPHA(SpongeKernelEntry{                        \
-        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 0, sponge_kernel<TuField, T, ALPHA, 5>, \
+        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 0, PSD_MAX_BLOCK(5), sponge_kernel<TuField, T, ALPHA, 5>, \
         "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ">"}); \
     static SpongeKernelRegistrar g_regr_##T##_##ALPHA(SpongeKernelEntry{                       \
-        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 1,                                      \
+        TuField::kFieldId, T, ALPHA, 5, PSD_POOL_KIND, 1, PSD_MAX_BLOCK(5),                    \
         sponge_kernel<TuField, T, ALPHA, 5, PSD_POOL_KIND, true>,                              \
         "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=5" PSD_POOL_TAG ",ragged>"});
 

@@ -35,14 +35,14 @@ static ConstPoolRegistrar g_pool(TuField::kFieldId, PSD_TU_T, tu_upload);
 
 #define PSD_REG(ALPHA, VARIANT)                                                                       \
     static SpongeKernelRegistrar g_reg_##ALPHA##_##VARIANT(SpongeKernelEntry{                         \
-        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 0,                                \
+        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 0, PSD_MAX_BLOCK(VARIANT),        \
         sponge_kernel<TuField, PSD_TU_T, ALPHA, VARIANT>,                                             \
         "sponge_kernel<" PSD_TU_FNAME ",t=" PSD_STR(PSD_TU_T) ",alpha=" #ALPHA ",variant=" #VARIANT PSD_POOL_TAG ">"});
 // the same kernel with per-sponge absorb lengths (ragged batches): registered for the forms a context ends
 // up running by default, so that a ragged call never changes the algorithm
 #define PSD_REG_RAGGED(ALPHA, VARIANT)                                                                \
     static SpongeKernelRegistrar g_regr_##ALPHA##_##VARIANT(SpongeKernelEntry{                        \
-        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 1,                                \
+        TuField::kFieldId, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, 1, PSD_MAX_BLOCK(VARIANT),        \
         sponge_kernel<TuField, PSD_TU_T, ALPHA, VARIANT, PSD_POOL_KIND, true>,                        \
         "sponge_kernel<" PSD_TU_FNAME ",t=" PSD_STR(PSD_TU_T) ",alpha=" #ALPHA ",variant=" #VARIANT PSD_POOL_TAG ",ragged>"});
 

@@ -21,7 +21,7 @@ typedef Bls12381Fr TuField;
 
 #define PSD_REG_TC(T, ALPHA)                                                                  \
     static SpongeKernelRegistrar g_reg_tc_##T##_##ALPHA(SpongeKernelEntry{                    \
-        TuField::kFieldId, T, ALPHA, 6, 1, 0, sponge_kernel<TuField, T, ALPHA, 6>,            \
+        TuField::kFieldId, T, ALPHA, 6, 1, 0, PSD_MAX_BLOCK(6), sponge_kernel<TuField, T, ALPHA, 6>, \
         "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=6,smem>"});
 
 PSD_REG_TC(3, 5)
