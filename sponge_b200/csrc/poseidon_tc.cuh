@@ -34,7 +34,7 @@
 namespace psd {
 
 constexpr uint32_t kTcFragBytes = 1024;   // one constant: 4 n-tiles x 32 lanes x (b0, b1)
-constexpr uint32_t kTcKBytes = 128;       // one additive constant: 4 n-tiles x 4 column pairs x 2 x s32
+constexpr uint32_t kTcKBytes = 256;       // one additive constant: 4 n-tiles x 4 column pairs x (k0, k1, k0, k1) s32
 // per-warp shared-memory scratch: two A tiles (32 sponges x 32 bytes, rows padded to 48) and two column-sum
 // exchange tiles (32 sponges x 16 words, rows padded to 20 words); consecutive uses alternate between the two
 // copies so that only the write -> read direction needs a warp barrier
@@ -108,19 +108,26 @@ __device__ __forceinline__ void tc_pack(uint32_t (&a)[2][4], const uint32_t* x, 
     }
 }
 
-// accumulators <- the additive constant's bytes (columns 8 nt + 2 tg, + 1 of every row this thread holds)
-__device__ __forceinline__ void tc_init(int (&acc)[2][4][4], const unsigned char* kfrag, const TcWarp& w) {
+// d = a x b + c with c given separately (the first k-step of an output value: c = the additive constant's bytes,
+// so the accumulators need no initialising moves; the table stores (k0, k1, k0, k1) so that one 128-bit load
+// delivers the four consecutive registers the instruction wants)
+__device__ __forceinline__ void tc_mma_c(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, const int4& c) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "r"(c.x), "r"(c.y), "r"(c.z), "r"(c.w));
+}
+
+// accumulators = K + bytes(value behind the A fragments) x Tab_c: the additive constant's bytes (columns 8 nt + 2 tg,
+// + 1 of every row this thread holds; the same for all its rows) enter as the C operand of the first k-step
+__device__ __forceinline__ void tc_mac_first(int (&acc)[2][4][4], const uint32_t (&a)[2][4], const unsigned char* frag,
+                                             const unsigned char* kfrag, const TcWarp& w) {
     const int tg = w.lane & 3;
 #pragma unroll
     for (int nt = 0; nt < 4; nt++) {
-        const int2 v = __ldg(reinterpret_cast<const int2*>(kfrag) + nt * 4 + tg);
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) {
-            acc[mt][nt][0] = v.x;
-            acc[mt][nt][1] = v.y;
-            acc[mt][nt][2] = v.x;
-            acc[mt][nt][3] = v.y;
-        }
+        const int4 k = __ldg(reinterpret_cast<const int4*>(kfrag) + nt * 4 + tg);
+        const uint2 b = __ldg(reinterpret_cast<const uint2*>(frag) + nt * 32 + w.lane);
+        tc_mma_c(acc[0][nt], a[0], b.x, b.y, k);
+        tc_mma_c(acc[1][nt], a[1], b.x, b.y, k);
     }
 }
 
@@ -158,18 +165,34 @@ __device__ __forceinline__ void tc_sweep(uint32_t* out, const int (&acc)[2][4][4
         const uint4 v = *reinterpret_cast<const uint4*>(tile + w.lane * kTcCRow + k * 16);
         Q[k][0] = v.x; Q[k][1] = v.y; Q[k][2] = v.z; Q[k][3] = v.w;
     }
-    // value = sum_{nt, k} Q[k][nt] 2^(64 nt + 16 k)  ->  v[0..8]
+    // value = sum_{nt, k} Q[k][nt] 2^(64 nt + 16 k) = X + (Y << 16) with
+    //   X = limbs (Q[0][0], Q[2][0], Q[0][1], Q[2][1], ...)   (column pairs at bit offsets 0 and 32 of each 64-bit word)
+    //   Y = limbs (Q[1][0], Q[3][0], Q[1][1], Q[3][1], ...)   (offsets 16 and 48)
+    // every Q is below 2^32, so X and Y are plain 256-bit numbers: nine funnel shifts and one carry chain
     uint32_t v[9];
-    uint64_t carry = 0;
+    {
+        uint32_t ys[9];
+        ys[0] = Q[1][0] << 16;
 #pragma unroll
-    for (int nt = 0; nt < 4; nt++) {
-        const uint64_t lo = (uint64_t)Q[0][nt] + ((uint64_t)Q[1][nt] << 16) + carry;          // < 2^50
-        const uint64_t hi = (uint64_t)Q[2][nt] + ((uint64_t)Q[3][nt] << 16) + (lo >> 32);     // < 2^50
-        v[2 * nt] = (uint32_t)lo;
-        v[2 * nt + 1] = (uint32_t)hi;
-        carry = hi >> 32;
+        for (int k = 1; k < 8; k++) {
+            const uint32_t lo = (k & 1) ? Q[1][k >> 1] : Q[3][(k >> 1) - 1];   // limb k - 1 of Y
+            const uint32_t hi = (k & 1) ? Q[3][k >> 1] : Q[1][k >> 1];         // limb k of Y
+            ys[k] = __funnelshift_l(lo, hi, 16);
+        }
+        ys[8] = Q[3][3] >> 16;
+        asm("add.cc.u32 %0, %9, %18;\n\t"
+            "addc.cc.u32 %1, %10, %19;\n\t"
+            "addc.cc.u32 %2, %11, %20;\n\t"
+            "addc.cc.u32 %3, %12, %21;\n\t"
+            "addc.cc.u32 %4, %13, %22;\n\t"
+            "addc.cc.u32 %5, %14, %23;\n\t"
+            "addc.cc.u32 %6, %15, %24;\n\t"
+            "addc.cc.u32 %7, %16, %25;\n\t"
+            "addc.u32 %8, %17, 0;"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8])
+            : "r"(Q[0][0]), "r"(Q[2][0]), "r"(Q[0][1]), "r"(Q[2][1]), "r"(Q[0][2]), "r"(Q[2][2]), "r"(Q[0][3]), "r"(Q[2][3]),
+              "r"(ys[8]), "r"(ys[0]), "r"(ys[1]), "r"(ys[2]), "r"(ys[3]), "r"(ys[4]), "r"(ys[5]), "r"(ys[6]), "r"(ys[7]));
     }
-    v[8] = (uint32_t)carry;
     // Montgomery row: (V + m p) / 2^32, m = -V / p mod 2^32.  First the even limbs of p onto columns 0..7 (column 0
     // becomes zero), then the odd limbs onto columns 1..8; the carry out of column 8 is provably zero
     // (V + m p < 2^273 + 2^286 < 2^288).
@@ -196,9 +219,9 @@ __device__ __forceinline__ void tc_full_round(uint32_t (&st)[T][8], const unsign
     int acc[2][4][4];
 #pragma unroll
     for (int i = 0; i < T; i++) {
-        tc_init(acc, kp + i * kTcKBytes, w);
+        tc_mac_first(acc, aX[0], mat + (i * T) * kTcFragBytes, kp + i * kTcKBytes, w);
 #pragma unroll
-        for (int j = 0; j < T; j++) tc_mac(acc, aX[j], mat + (i * T + j) * kTcFragBytes, w);
+        for (int j = 1; j < T; j++) tc_mac(acc, aX[j], mat + (i * T + j) * kTcFragBytes, w);
         tc_sweep<F>(st[i], acc, w);
     }
 }
@@ -212,8 +235,7 @@ template <class F, int T>
 __device__ __forceinline__ void tc_row0(uint32_t* st0, const uint32_t (&aY)[2][4], const uint32_t (&aL)[T - 1][2][4],
                                         const unsigned char* m00, const unsigned char* part, const unsigned char* kp, TcWarp& w) {
     int acc[2][4][4];
-    tc_init(acc, kp, w);
-    tc_mac(acc, aY, m00, w);
+    tc_mac_first(acc, aY, m00, kp, w);
 #pragma unroll
     for (int j = 1; j < T; j++) tc_mac(acc, aL[j - 1], part + (j - 1) * kTcFragBytes, w);
     tc_sweep<F>(st0, acc, w);
@@ -226,8 +248,7 @@ __device__ __forceinline__ void tc_lanes(uint32_t (&st)[T][8], const uint32_t (&
 #pragma unroll
     for (int j = 1; j < T; j++) {
         int acc[2][4][4];
-        tc_init(acc, kp + j * kTcKBytes, w);
-        tc_mac(acc, aY, part + (T - 1 + j - 1) * kTcFragBytes, w);
+        tc_mac_first(acc, aY, part + (T - 1 + j - 1) * kTcFragBytes, kp + j * kTcKBytes, w);
         tc_mac(acc, aL[j - 1], ident, w);
         uint32_t lane[8];
         tc_sweep<F>(lane, acc, w);
@@ -272,7 +293,6 @@ __device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc&
         for (uint32_t i = 0; i + 1 < rp; i++) {
             tc_row0<F, T>(st[0], aY, aL, m00, part, kp, w);
             // independent of each other: the S-box of round i + 1 and the lane updates of round i
-            uint32_t aYn[2][4];
 #if PSD_TC_PIPELINE
             tc_sbox<F, ALPHA>(st[0]);
             tc_lanes<F, T, true>(st, aY, aL, ident, part, kp, w);
@@ -281,11 +301,7 @@ __device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc&
             __syncwarp();   // keeps the two phases apart in the schedule (fewer live registers, more warps)
             tc_sbox<F, ALPHA>(st[0]);
 #endif
-            tc_pack(aYn, st[0], w);
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++)
-#pragma unroll
-                for (int q = 0; q < 4; q++) aY[mt][q] = aYn[mt][q];
+            tc_pack(aY, st[0], w);   // the lane updates above were the last readers of the old fragments
             kp += T * kTcKBytes;
             part += 2 * (T - 1) * kTcFragBytes;
         }

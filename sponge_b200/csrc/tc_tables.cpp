@@ -46,15 +46,16 @@ void push_frag(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[
 }
 
 // accumulator start values of the additive constant with Montgomery residue k_mont: bytes of K' = K 2^32 mod p;
-// for n-tile nt and column pair tg two little-endian s32: K'[8 nt + 2 tg], K'[8 nt + 2 tg + 1]
+// for n-tile nt and column pair tg four little-endian s32: K'[8 nt + 2 tg], K'[8 nt + 2 tg + 1], and the same
+// pair again (the C operand of mma.m16n8k32 holds two rows of the pair)
 void push_kfrag(std::vector<uint8_t>& img, const HostField& f, const Fe& pow32_mont, const Fe& k_mont) {
     // k_mont IS the integer to be added to the state (a residue below p); K' = k_mont * 2^32 mod p as an integer:
     // hf_mul(a, b) = a b / R, so with b = 2^32 R mod p (the Montgomery form of 2^32) the product is a 2^32 mod p.
     const Fe kp = hf_mul(f, k_mont, pow32_mont);
     for (int nt = 0; nt < 4; nt++)
         for (int tg = 0; tg < 4; tg++)
-            for (int e = 0; e < 2; e++) {
-                const uint32_t v = byte_of(kp, 8 * nt + 2 * tg + e);
+            for (int e = 0; e < 4; e++) {
+                const uint32_t v = byte_of(kp, 8 * nt + 2 * tg + (e & 1));
                 for (int b = 0; b < 4; b++) img.push_back((uint8_t)(v >> (8 * b)));
             }
 }
@@ -164,7 +165,7 @@ void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const 
     uint64_t col[32];
     for (int c = 0; c < 32; c++) {
         const int nt = c / 8, tg = (c % 8) / 2, e = c % 2;
-        const uint8_t* q = kfrag + ((nt * 4 + tg) * 2 + e) * 4;
+        const uint8_t* q = kfrag + ((nt * 4 + tg) * 4 + e) * 4;
         col[c] = (uint64_t)q[0] | ((uint64_t)q[1] << 8) | ((uint64_t)q[2] << 16) | ((uint64_t)q[3] << 24);
     }
     for (uint32_t j = 0; j < n_terms; j++)
