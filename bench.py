@@ -67,10 +67,11 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--log-n", type=int, default=None, help="override log2(units per GPU)")
-    ap.add_argument("--variant", type=int, default=6,
-                    help="0 = dense kernel, 1 = optimised unrolled, 2 = optimised compact, "
-                         "3 = compact + digit-table constant products, 5 = integer S-box + FP64-pipe linear "
-                         "layer (library default; BN254 t<=3, otherwise runs as 3)")
+    ap.add_argument("--variant", type=int, default=None,
+                    help="kernel variant to request instead of the library's default (BN254: 6 = integer S-box + "
+                         "tensor-core linear layer; BLS12-381: 5 -> 3 = all-integer with digit tables).  0 = dense "
+                         "reference-order kernel, 1 = optimised unrolled, 2 = optimised compact, 3 = compact + "
+                         "digit-table constant products, 5 = integer S-box + FP64-pipe linear layer")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target duration of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg")
@@ -420,7 +421,8 @@ def main():
 
     cfg = product_config(w)
     ctx = cfg.context(local_rank)
-    ctx.set_variant(args.variant)
+    if args.variant is not None:
+        ctx.set_variant(args.variant)
     stream = torch.cuda.current_stream()
     sptr = stream.cuda_stream
     units, perms_per_unit = units_and_perms(name, w, n)
