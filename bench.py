@@ -247,7 +247,7 @@ def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
                                          instructions per permutation by pipe, registers, DRAM bytes per launch.
     The ncu numbers are used only if their SASS fingerprint equals this build's kernel (else `stale`).  From them
     and THIS run's time and clock:  issue_frac = warp instructions issued / issue slots, and
-    heavy_pipe_frac = (4 N_imad_wide + 2 N_imad + 2 N_fp64) warp-cycles / cycles -- the share of the time the
+    heavy_pipe_frac = (4 (N_imad_wide + N_imad_hi) + 2 N_imad + 2 N_fp64) warp-cycles / cycles -- the share of the time the
     half-rate multiplier datapaths (integer multiply, FP64) are busy under the cycle model of DESIGN.md section 4.
     Returns (exec dict, dram bytes per launch or None)."""
     import re
@@ -281,7 +281,7 @@ def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
     crec = counts.get(key)
     traffic = None
     if crec:
-        fresh = bool(srec) and crec.get("sass_sha256") == srec["sass_sha256"]
+        fresh = bool(srec) and crec.get("opcode_sha256") == srec.get("opcode_sha256")
         out["ncu_capture"] = crec.get("source")
         out["ncu_capture_matches_this_build"] = fresh
         per = crec.get("warp_inst_per_perm", {})
@@ -292,10 +292,10 @@ def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
             sm_count = crec.get("sm_count", 148)
             cycles = ms_per_step * 1e-3 * sm_mhz * 1e6                   # per SM sub-partition, this run
             warp_perms = perms_per_step_gpu / 32.0 / (sm_count * 4)         # per SM sub-partition
-            heavy = 4 * per.get("imad_wide", 0) + 2 * per.get("imad", 0) + 2 * per.get("fp64", 0)
+            heavy = 4 * (per.get("imad_wide", 0) + per.get("imad_hi", 0)) + 2 * per.get("imad", 0) + 2 * per.get("fp64", 0)
             out["issue_frac"] = per.get("total", 0) * warp_perms / cycles
             out["heavy_pipe_frac"] = heavy * warp_perms / cycles
-            out["w_exec_imul_per_perm"] = per.get("imad_wide", 0) + per.get("imad", 0)
+            out["w_exec_imul_per_perm"] = per.get("imad_wide", 0) + per.get("imad_hi", 0) + per.get("imad", 0)
             out["fp64_inst_per_perm"] = per.get("fp64", 0)
         if crec.get("workload") == name and crec.get("log_n") == log_n and fresh:
             traffic = crec.get("dram_bytes_per_launch")

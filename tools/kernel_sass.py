@@ -5,8 +5,10 @@ usage: tools/kernel_sass.py <out.json> <object.o> [<object.o> ...]
 
 For every `sponge_kernel<...>` entry in the given objects (cuobjdump -sass):
   * `sass_sha256`   fingerprint of the instruction stream (opcodes + operands, addresses and encodings
-                    stripped).  bench.py uses it to decide whether the ncu-measured per-permutation instruction
-                    counts in profiles/ (tools/ncu_counts.py) were taken from THIS build of the kernel;
+                    stripped); `opcode_sha256` the same over the opcode sequence alone, which is what an ncu report's
+                    source page reproduces exactly (it prints absolute branch targets).  bench.py uses the latter to
+                    decide whether the ncu-measured per-permutation instruction counts in profiles/
+                    (tools/ncu_counts.py) were taken from THIS build of the kernel;
   * `instructions`  static instruction count and the multiply / FP64 / load mix of the whole kernel;
   * `loops`         every backward branch's body [target, branch] with the same mix -- the partial-round loop of
                     the variant-5 kernels is the largest body without an inner loop (straight-line code).
@@ -60,7 +62,9 @@ def analyse(obj):
                 d = mix([op for _, op, _ in ins[s:e + 1]])
                 d.update(first=f"{ins[s][0]:#x}", last=f"{ins[e][0]:#x}", has_inner_loop=inner)
                 lrec.append(d)
-            kernels[fn] = dict(sass_sha256=hashlib.sha256(text.encode()).hexdigest(), instructions=mix([op for _, op, _ in ins]),
+            ops = "\n".join(op for _, op, _ in ins)
+            kernels[fn] = dict(sass_sha256=hashlib.sha256(text.encode()).hexdigest(),
+                               opcode_sha256=hashlib.sha256(ops.encode()).hexdigest(), instructions=mix([op for _, op, _ in ins]),
                                loops=lrec)
 
     for line in out.splitlines():
@@ -92,7 +96,7 @@ def main():
     for obj in objs:
         st = os.stat(obj)
         cache = obj + ".sass.json"
-        key = f"{st.st_size}:{st.st_mtime_ns}"
+        key = f"v2:{st.st_size}:{st.st_mtime_ns}"
         rec = None
         if os.path.exists(cache):
             try:

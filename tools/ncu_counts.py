@@ -12,6 +12,7 @@ bench.py can tell whether the numbers belong to the library it is running.  Also
 (launch facts, pipe activity, stall reasons, DRAM traffic) for profiles/."""
 import argparse
 import collections
+import hashlib
 import csv
 import json
 import re
@@ -63,12 +64,14 @@ def main():
     si, ei = hdr.index("Source"), hdr.index("Instructions Executed")
     stall_cols = [(i, h) for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
     by_class, stalls, total = collections.Counter(), collections.Counter(), 0
+    opcodes = []
     for r in rows[1:]:
         if len(r) <= ei:
             continue
         m = re.match(r"\s*(@!?U?P\d+\s+)?([A-Z0-9_.]+)", r[si])
         if not m:
             continue
+        opcodes.append(m.group(2))
         try:
             n = int(float(r[ei]))
         except ValueError:
@@ -106,7 +109,10 @@ def main():
 
     sass = json.load(open(a.kernel_sass))
     rec = dict(workload=a.workload, log_n=a.log_n, perms_per_launch=a.perms_per_launch, source=a.source or a.report,
-               sass_sha256=(sass.get(kernel) or {}).get("sass_sha256"),
+               # fingerprint of the CAPTURED kernel's opcode sequence (what tools/kernel_sass.py computes for a build)
+               opcode_sha256=hashlib.sha256("\n".join(opcodes).encode()).hexdigest(),
+               matches_build_at_processing_time=(sass.get(kernel) or {}).get("opcode_sha256") ==
+               hashlib.sha256("\n".join(opcodes).encode()).hexdigest(),
                warp_inst_per_perm={k: round(x, 2) for k, x in sorted(per.items())},
                registers_per_thread=metric("launch__registers_per_thread", lambda s: int(float(s))),
                block_size=metric("launch__block_size", lambda s: int(float(s))),
