@@ -51,6 +51,11 @@ extern "C" {
     pub fn psd_permute_batch(ctx: *mut psd_ctx, states: *mut u64, n: usize, layout: c_int, repr: c_int, mem: c_int, stream: *mut c_void) -> c_int;
     pub fn psd_absorb_squeeze_batch(ctx: *mut psd_ctx, inputs: *const u64, n: usize, n_absorb: u32, n_squeeze: u32, outputs: *mut u64, layout: c_int, repr: c_int, mem: c_int, stream: *mut c_void) -> c_int;
     pub fn psd_merkle_root(ctx: *mut psd_ctx, leaves: *const u64, n_leaves: usize, root: *mut u64, repr: c_int, mem: c_int, stream: *mut c_void) -> c_int;
+    pub fn psd_absorb_squeeze_ragged_batch(ctx: *mut psd_ctx, inputs: *const u64, offsets: *const u64, n: usize, n_squeeze: u32, outputs: *mut u64, repr: c_int, mem: c_int, stream: *mut c_void) -> c_int;
+    pub fn psd_device_count() -> c_int;
+    pub fn psd_permute_batch_multi(ctxs: *const *mut psd_ctx, n_gpus: c_int, states: *mut u64, n: usize, layout: c_int, repr: c_int) -> c_int;
+    pub fn psd_absorb_squeeze_batch_multi(ctxs: *const *mut psd_ctx, n_gpus: c_int, inputs: *const u64, n: usize, n_absorb: u32, n_squeeze: u32, outputs: *mut u64, layout: c_int, repr: c_int) -> c_int;
+    pub fn psd_merkle_root_multi(ctxs: *const *mut psd_ctx, n_gpus: c_int, leaves_per_gpu: *const *const u64, leaves_per_gpu_n: usize, root: *mut u64, repr: c_int, mem: c_int, streams: *const *mut c_void) -> c_int;
     pub fn psd_host_alloc(bytes: usize, out: *mut *mut c_void) -> c_int;
     pub fn psd_host_free(p: *mut c_void);
 }
