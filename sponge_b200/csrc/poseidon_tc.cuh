@@ -49,6 +49,7 @@ struct TcDesc {
     uint32_t pre_off;     // [T][T] fragments of M_pre
     uint32_t ident_off;   // fragment of the constant 1
     uint32_t part_off;    // [partial][2(T-1)] fragments: w_1.., v_1.. per partial round
+    uint32_t pair_off;    // [partial / 2] fragments: c_q = sum_j w_j(i+1) v_j(i) for the q-th PAIR of partial rounds (i, i+1)
     uint32_t k_off;       // [rounds][T] additive constants (accumulator start values), execution order
 };
 
@@ -261,6 +262,44 @@ __device__ __forceinline__ void tc_lanes(uint32_t (&st)[T][8], const uint32_t (&
     }
 }
 
+// Partial rounds are run in PAIRS (i, i+1): between partial rounds the lanes change only by a multiple of the S-box
+// output, so the second row 0 of a pair can take the lanes as they were BEFORE the pair plus one extra term,
+//   row0(i+1) = M00 y1 + (sum_j w_j(i+1) v_j(i)) y0 + sum_j w_j(i+1) s_j + k,
+// and the lanes are brought up to date once per pair:  s_j <- 1 s_j + v_j(i) y0 + v_j(i+1) y1.  Per pair and lane that is
+// one sweep and one re-pack instead of two, for one more k-step in the second row.
+template <class F, int T>
+__device__ __forceinline__ void tc_row0_second(uint32_t* st0, const uint32_t (&aY1)[2][4], const uint32_t (&aY0)[2][4],
+                                               const uint32_t (&aL)[T - 1][2][4], const unsigned char* m00, const unsigned char* pair,
+                                               const unsigned char* part_next, const unsigned char* kp_next, TcWarp& w) {
+    int acc[2][4][4];
+    tc_mac_first(acc, aY1, m00, kp_next, w);
+    tc_mac(acc, aY0, pair, w);
+#pragma unroll
+    for (int j = 1; j < T; j++) tc_mac(acc, aL[j - 1], part_next + (j - 1) * kTcFragBytes, w);
+    tc_sweep<F>(st0, acc, w);
+}
+
+template <class F, int T, bool REPACK>
+__device__ __forceinline__ void tc_lanes_pair(uint32_t (&st)[T][8], const uint32_t (&aY0)[2][4], const uint32_t (&aY1)[2][4],
+                                              uint32_t (&aL)[T - 1][2][4], const unsigned char* ident, const unsigned char* part,
+                                              const unsigned char* part_next, const unsigned char* kp_next, TcWarp& w) {
+#pragma unroll
+    for (int j = 1; j < T; j++) {
+        int acc[2][4][4];
+        tc_mac_first(acc, aY1, part_next + (T - 1 + j - 1) * kTcFragBytes, kp_next + j * kTcKBytes, w);
+        tc_mac(acc, aY0, part + (T - 1 + j - 1) * kTcFragBytes, w);
+        tc_mac(acc, aL[j - 1], ident, w);
+        uint32_t lane[8];
+        tc_sweep<F>(lane, acc, w);
+        if (REPACK) {
+            tc_pack(aL[j - 1], lane, w);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; k++) st[j][k] = lane[k];
+        }
+    }
+}
+
 template <class F, int T, int ALPHA>
 __device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, TcWarp& w) {
     static_assert(ALPHA == 5 || ALPHA == 17, "variant 6: alpha 5 or 17");
@@ -281,34 +320,54 @@ __device__ __forceinline__ void permute_tc(uint32_t (&st)[T][8], const PermDesc&
     }
 
     if (rp) {
-        uint32_t aL[T - 1][2][4], aY[2][4];
+        constexpr uint32_t kRoundK = T * kTcKBytes, kRoundPart = 2 * (T - 1) * kTcFragBytes;
+        uint32_t aL[T - 1][2][4], aY0[2][4];
 #pragma unroll
         for (int j = 1; j < T; j++) tc_pack(aL[j - 1], st[j], w);
         const unsigned char* part = w.tab + td.part_off;
+        const unsigned char* pair = w.tab + td.pair_off;
         const unsigned char* m00 = w.tab + td.mat_off;
         const unsigned char* ident = w.tab + td.ident_off;
+        const uint32_t pairs = rp >> 1;
         tc_sbox<F, ALPHA>(st[0]);
-        tc_pack(aY, st[0], w);
-#pragma unroll 1
-        for (uint32_t i = 0; i + 1 < rp; i++) {
-            tc_row0<F, T>(st[0], aY, aL, m00, part, kp, w);
-            // independent of each other: the S-box of round i + 1 and the lane updates of round i
-#if PSD_TC_PIPELINE
-            tc_sbox<F, ALPHA>(st[0]);
-            tc_lanes<F, T, true>(st, aY, aL, ident, part, kp, w);
-#else
-            tc_lanes<F, T, true>(st, aY, aL, ident, part, kp, w);
-            __syncwarp();   // keeps the two phases apart in the schedule (fewer live registers, more warps)
-            tc_sbox<F, ALPHA>(st[0]);
-#endif
-            tc_pack(aY, st[0], w);   // the lane updates above were the last readers of the old fragments
-            kp += T * kTcKBytes;
-            part += 2 * (T - 1) * kTcFragBytes;
+        tc_pack(aY0, st[0], w);
+        if (rp & 1) {
+            // an odd number of partial rounds: the first one on its own
+            tc_row0<F, T>(st[0], aY0, aL, m00, part, kp, w);
+            if (pairs) {
+                tc_sbox<F, ALPHA>(st[0]);
+                tc_lanes<F, T, true>(st, aY0, aL, ident, part, kp, w);
+                tc_pack(aY0, st[0], w);
+            } else {
+                tc_lanes<F, T, false>(st, aY0, aL, ident, part, kp, w);
+            }
+            kp += kRoundK;
+            part += kRoundPart;
         }
-        // last partial round: the updated lanes are needed as limbs again (full rounds follow)
-        tc_row0<F, T>(st[0], aY, aL, m00, part, kp, w);
-        tc_lanes<F, T, false>(st, aY, aL, ident, part, kp, w);
-        kp += T * kTcKBytes;
+        if (pairs) {
+            uint32_t aY1[2][4];
+#pragma unroll 1
+            for (uint32_t q = 0; q + 1 < pairs; q++) {
+                tc_row0<F, T>(st[0], aY0, aL, m00, part, kp, w);
+                tc_sbox<F, ALPHA>(st[0]);
+                tc_pack(aY1, st[0], w);
+                tc_row0_second<F, T>(st[0], aY1, aY0, aL, m00, pair, part + kRoundPart, kp + kRoundK, w);
+                // independent of each other: the S-box of the next pair's first round and this pair's lane updates
+                tc_sbox<F, ALPHA>(st[0]);
+                tc_lanes_pair<F, T, true>(st, aY0, aY1, aL, ident, part, part + kRoundPart, kp + kRoundK, w);
+                tc_pack(aY0, st[0], w);
+                kp += 2 * kRoundK;
+                part += 2 * kRoundPart;
+                pair += kTcFragBytes;
+            }
+            // last pair: the updated lanes are needed as limbs again (full rounds follow)
+            tc_row0<F, T>(st[0], aY0, aL, m00, part, kp, w);
+            tc_sbox<F, ALPHA>(st[0]);
+            tc_pack(aY1, st[0], w);
+            tc_row0_second<F, T>(st[0], aY1, aY0, aL, m00, pair, part + kRoundPart, kp + kRoundK, w);
+            tc_lanes_pair<F, T, false>(st, aY0, aY1, aL, ident, part, part + kRoundPart, kp + kRoundK, w);
+            kp += 2 * kRoundK;
+        }
     }
 
 #pragma unroll 1

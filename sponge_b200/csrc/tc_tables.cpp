@@ -68,8 +68,9 @@ bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why) {
         return false;
     };
     if (t < 2 || t > 5) return no("width outside [2,5]");
-    // column sums: 32 t products of two bytes plus one constant byte; pair-combining needs sum * 257 < 2^32
-    const uint64_t colmax = 32ull * t * 255 * 255 + 255;
+    // column sums: at most 32 (t + 1) products of two bytes (the second row 0 of a pair of partial rounds has t + 1
+    // terms) plus one constant byte; pair-combining needs sum * 257 < 2^32
+    const uint64_t colmax = 32ull * (t + 1) * 255 * 255 + 255;
     if (colmax * 257 >= (1ull << 32)) return no("column sums too large for the pair-combine");
     // sweep input V < colmax * 256^32 * 256/255 ; result (V + m p) / 2^32 < V / 2^32 + p must stay below 2^256 and,
     // for the lazy S-box (BN254), inside its operand range 2 a + p < 2^256 with the output below 2^256
@@ -138,6 +139,13 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
     for (uint32_t i = 0; i < rp; i++) {
         for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j]);
         for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j]);
+    }
+    // pairs of partial rounds (an odd count leaves the FIRST round on its own): c_q = sum_j w_j(i+1) v_j(i)
+    td.pair_off = here();
+    for (uint32_t i = rp & 1; i + 1 < rp; i += 2) {
+        Fe c = hf_zero();
+        for (uint32_t j = 0; j < n; j++) c = hf_add(f, c, hf_mul(f, w[i + 1][j], v[i][j]));
+        push_frag(img, f, pow_mont, c);
     }
     // additive constants in execution order, t per round: what round r's outputs receive is what round r + 1
     // adds before its S-boxes

@@ -326,7 +326,10 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
     for (uint32_t r = 0; r < half; r++) full_round(tab + ((r + 1 == half && rp) ? td.pre_off : td.mat_off));
     if (rp) {
         const uint8_t* part = tab + td.part_off;
-        for (uint32_t i = 0; i < rp; i++) {
+        const uint8_t* pair = tab + td.pair_off;
+        const uint32_t round_k = T * kTcKBytes, round_part = 2 * (T - 1) * kTcFragBytes;
+        // one round on its own: row 0, then every lane <- 1 lane + v y
+        auto single = [&]() {
             tc_sbox<F, ALPHA>(st[0]);
             uint32_t terms[T][8];
             const uint8_t* frags[T];
@@ -346,8 +349,55 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                 tc_host_row(hf, &two[0][0], 2, fr, kp + j * kTcKBytes, st[j]);
             }
             memcpy(st[0], n0, 32);
-            kp += T * kTcKBytes;
-            part += 2 * (T - 1) * kTcFragBytes;
+            kp += round_k;
+            part += round_part;
+        };
+        if (rp & 1) single();
+        // pairs (i, i+1): the second row 0 takes the lanes as they were before the pair plus c_q y0; the lanes are
+        // brought up to date once per pair
+        for (uint32_t q = 0; q < rp / 2; q++) {
+            uint32_t y0[8], y1[8], x1[8], x2[8];
+            tc_sbox<F, ALPHA>(st[0]);
+            memcpy(y0, st[0], 32);
+            {
+                uint32_t terms[T][8];
+                const uint8_t* frags[T];
+                memcpy(terms[0], y0, 32);
+                frags[0] = tab + td.mat_off;
+                for (int j = 1; j < T; j++) {
+                    memcpy(terms[j], st[j], 32);
+                    frags[j] = part + (j - 1) * kTcFragBytes;
+                }
+                tc_host_row(hf, &terms[0][0], T, frags, kp, x1);
+            }
+            memcpy(y1, x1, 32);
+            tc_sbox<F, ALPHA>(y1);
+            {
+                uint32_t terms[T + 1][8];
+                const uint8_t* frags[T + 1];
+                memcpy(terms[0], y1, 32);
+                frags[0] = tab + td.mat_off;
+                memcpy(terms[1], y0, 32);
+                frags[1] = pair;
+                for (int j = 1; j < T; j++) {
+                    memcpy(terms[j + 1], st[j], 32);
+                    frags[j + 1] = part + round_part + (j - 1) * kTcFragBytes;
+                }
+                tc_host_row(hf, &terms[0][0], T + 1, frags, kp + round_k, x2);
+            }
+            for (int j = 1; j < T; j++) {
+                uint32_t three[3][8];
+                memcpy(three[0], y1, 32);
+                memcpy(three[1], y0, 32);
+                memcpy(three[2], st[j], 32);
+                const uint8_t* fr[3] = {part + round_part + (T - 1 + j - 1) * kTcFragBytes, part + (T - 1 + j - 1) * kTcFragBytes,
+                                        tab + td.ident_off};
+                tc_host_row(hf, &three[0][0], 3, fr, kp + round_k + j * kTcKBytes, st[j]);
+            }
+            memcpy(st[0], x2, 32);
+            kp += 2 * round_k;
+            part += 2 * round_part;
+            pair += kTcFragBytes;
         }
     }
     for (uint32_t r = half + rp; r < d.total; r++) full_round(tab + td.mat_off);
