@@ -47,6 +47,11 @@ for f in 0 1; do
   o=$OBJ/tu_tc_${f}.o
   if newer $o $SRC/tu_tc.cu $HDRS; then run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_POOL_SHARED=1 -c -o $o $SRC/tu_tc.cu; fi
 done
+# variant-7 unit (tcgen05 / TMEM form of the tensor-core linear layer)
+for f in 0 1; do
+  o=$OBJ/tu_tc5_${f}.o
+  if newer $o $SRC/tu_tc5.cu $HDRS; then run $NVCC $NVFLAGS -DPSD_TU_FIELD=$f -DPSD_POOL_SHARED=1 -c -o $o $SRC/tu_tc5.cu; fi
+done
 for u in misc_kernels api; do
   o=$OBJ/$u.o
   if newer $o $SRC/$u.cu $HDRS; then run $NVCC $NVFLAGS -c -o $o $SRC/$u.cu; fi
@@ -58,11 +63,11 @@ done
 fail=0
 for p in "${pids[@]:-}"; do [[ -n "$p" ]] && { wait "$p" || fail=1; }; done
 [[ $fail -eq 0 ]] || { echo "build failed" >&2; exit 1; }
-OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/tu_tc_0.o $OBJ/tu_tc_1.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o $OBJ/tc_tables.o"
+OBJS="$OBJ/api.o $OBJ/misc_kernels.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/tu_tc_0.o $OBJ/tu_tc_1.o $OBJ/tu_tc5_0.o $OBJ/tu_tc5_1.o $OBJ/params.o $OBJ/opt_constants.o $OBJ/fp52_tables.o $OBJ/tc_tables.o"
 for f in 0 1; do for t in $TS; do OBJS="$OBJS $OBJ/tu_${f}_${t}.o $OBJ/tu_${f}_${t}_smem.o"; done; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $LIB/libposeidon_b200.so $OBJS -Xcompiler -fPIC
 # static facts about the hot kernels (SASS fingerprints + instruction mix) for bench.py's roofline block
-python3 tools/kernel_sass.py $LIB/kernel_sass.json $OBJ/tu_tc_0.o $OBJ/tu_tc_1.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/tu_0_3.o $OBJ/tu_0_3_smem.o \
+python3 tools/kernel_sass.py $LIB/kernel_sass.json $OBJ/tu_tc5_0.o $OBJ/tu_tc5_1.o $OBJ/tu_tc_0.o $OBJ/tu_tc_1.o $OBJ/tu_fp52_0.o $OBJ/tu_fp52_0_smem.o $OBJ/tu_0_3.o $OBJ/tu_0_3_smem.o \
   $OBJ/tu_0_5.o $OBJ/tu_0_5_smem.o $OBJ/tu_1_3.o $OBJ/tu_1_3_smem.o
 # CPU oracle (test infrastructure)
 if newer oracle/liboracle.so oracle/poseidon_oracle.c; then

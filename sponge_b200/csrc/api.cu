@@ -115,6 +115,7 @@ enum : int { kPoolBank = 0, kPoolSmem = 1, kPoolGlobal = 2 };   // kPoolGlobal: 
 // pool keys beyond the state widths 2..9
 constexpr int kTcSmallKey = kFp52PoolKey + 1;   // variant 6: the few integer-side constants (staged to shared memory)
 constexpr int kTcTabKey = kFp52PoolKey + 2;     // variant 6: the table image in global memory
+constexpr int kTc5TabKey = kFp52PoolKey + 3;    // variant 7: the table image in the tcgen05 B-operand layout
 
 struct Placement {
     int device = 0, field = 0, key = 0;
@@ -132,7 +133,7 @@ struct DevicePool {
     std::vector<PoolSlot> used;    // sorted by off
     std::vector<Placement*> live;
 };
-static DevicePool g_pools[64][2][kTcTabKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool; then variant 6's two
+static DevicePool g_pools[64][2][kTc5TabKey + 1];   // [..][kFp52PoolKey]: the FP64-pipe unit's pool; then variant 6's two
 static std::once_flag g_misc_once[64];
 static inline uint32_t misc_one_off(int field) { return (uint32_t)field * 16; }
 static inline uint32_t misc_r2_off(int field) { return (uint32_t)field * 16 + 8; }
@@ -254,7 +255,10 @@ struct psd_ctx {
     TcDesc tcd{};
     Placement* pl_tc = nullptr;
     Placement* pl_tctab = nullptr;
-    int variant = 6;   // degrades to 5 / 3 / 2 / 0 by what the context has constants and kernels for (resolve_kernel)
+    // variant 7 (tu_tc5.cu): the same small image, its own table image (tcgen05 B-operand layout)
+    TcDesc tcd5{};
+    Placement* pl_tc5tab = nullptr;
+    int variant = 7;   // degrades to 5 / 3 / 2 / 0 by what the context has constants and kernels for (resolve_kernel)
     int sm_count = 0;
     // staging for PSD_MEM_HOST calls
     std::mutex stage_mu;
@@ -354,6 +358,7 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
         const uint64_t max_block = (uint64_t)k->max_block;
         const uint64_t per_sm = (n + sms - 1) / sms;
         cfg.block = (int)std::min<uint64_t>(max_block, std::max<uint64_t>(32, (per_sm + 31) / 32 * 32));
+        if (k->variant == 7) cfg.block = (cfg.block + 127) / 128 * 128;   // whole 128-sponge tiles
     } else if (k->variant == 5) {
         // Variant 5's partial-round body (1.5 K instructions) does not fit the instruction caches when
         // the warps of a scheduler sit at different places in it.  Warps of ONE block start together and
@@ -388,6 +393,13 @@ Resolved resolve_kernel(const psd_ctx* ctx, int ragged = 0) {
     Resolved r;
     // variant 6 uses warp-collective instructions, so it serves the lock-step calls only; ragged batches take
     // the next variant down
+    if (ctx->variant >= 7 && !ragged && ctx->pl_tc && ctx->pl_tc5tab && ctx->tcd5.ok) {
+        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 7, kPoolSmem, nullptr, 0);
+        if (k && k->variant == 7) {
+            r.k = k, r.pl = ctx->pl_tc, r.d = &ctx->tdesc;
+            return r;
+        }
+    }
     if (ctx->variant >= 6 && !ragged && ctx->pl_tc && ctx->pl_tctab && ctx->tcd.ok) {
         const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 6, kPoolSmem, nullptr, 0);
         if (k && k->variant == 6) {
@@ -433,6 +445,12 @@ psd_status launch(psd_ctx* ctx, const SpongeArgs& a, cudaStream_t stream) {
             static const int stagger = env_int("PSD_TC_STAGGER", 1500);   // cycles; measured on c2/c3: +0.5 % / +1.4 % over starting together
             b.tc_stagger = cfg.block >= 256 ? (uint32_t)std::max(0, stagger) : 0u;
             smem = ((smem + 127) & ~(size_t)127) + (size_t)(cfg.block / 32) * kTcWarpScratch;
+        }
+        if (k->variant == 7) {
+            // + the block's static tables, the tiles' A slots and table double buffers, the tiles' mbarriers
+            b.tc = ctx->tcd5;
+            b.tc_tab = reinterpret_cast<const unsigned char*>(ctx->pl_tc5tab->d_img);
+            smem = ((smem + 1023) & ~(size_t)1023) + tc5_smem_bytes(ctx->t, (uint32_t)cfg.block / 128);
         }
         const int ki = kernel_index(k);
         const uint64_t bit = 1ull << ctx->device;
@@ -753,7 +771,7 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     // Default request: the tensor-core form for BN254 (c2: 197 M perm/s against 174 M for variant 5); for BLS12-381
     // (alpha = 17 S-boxes with full reductions dominate) it measured SLOWER than the all-integer variant 3 on c5
     // (126 M against 169 M perm/s), so that field asks for 5 and gets 3; psd_ctx_set_variant(ctx, 6) still selects it.
-    ctx->variant = p->field == PSD_FIELD_BN254_FR ? 6 : 5;
+    ctx->variant = p->field == PSD_FIELD_BN254_FR ? 7 : 5;
 
     // constants -> Montgomery
     const Fe* ark = reinterpret_cast<const Fe*>(p->ark);
@@ -927,6 +945,19 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
                 if (ctx->pl_tc && ctx->pl_tctab) {
                     ctx->tdesc = sd;
                     ctx->tcd = td;
+                    // variant 7: the same tables in the tcgen05 B-operand layout, where tu_tc5.cu has a kernel
+                    const SpongeKernelEntry* k5 = find_kernel(p->field, (int)t, p->alpha, 7, kPoolSmem);
+                    if (k5 && k5->variant == 7 && k5->alpha == p->alpha && env_int("PSD_NO_TC5", 0) == 0) {
+                        TcDesc td5{};
+                        std::vector<uint8_t> tab5;
+                        build_tc_tables(*hf, t, p->full_rounds, p->partial_rounds, ctx->ark_mont, ctx->mds_mont, td5, tab5, 1);
+                        if (td5.ok) {
+                            std::vector<uint32_t> tab5w(tab5.size() / 4);
+                            memcpy(tab5w.data(), tab5.data(), tab5.size());
+                            ctx->pl_tc5tab = placement_acquire(device, p->field, kTc5TabKey, tab5w, false, false, &cerr, true);
+                            if (ctx->pl_tc5tab) ctx->tcd5 = td5;
+                        }
+                    }
                 } else if (cerr != cudaSuccess) {
                     psd_ctx_destroy(ctx);
                     return fail(PSD_ERR_CUDA, "uploading the variant-6 tables failed: %s", cudaGetErrorString(cerr));
@@ -1012,6 +1043,7 @@ static void ctx_teardown(psd_ctx* ctx) {
         placement_release(ctx->pl_fp);
         placement_release(ctx->pl_tc);
         placement_release(ctx->pl_tctab);
+        placement_release(ctx->pl_tc5tab);
     }
     delete ctx;
 }
@@ -1032,7 +1064,7 @@ psd_status psd_ctx_get_params(const psd_ctx* ctx, psd_params* out) {
 
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant) {
     if (!ctx) return fail(PSD_ERR_ARG, "null context");
-    if (variant < 0 || variant > 6) return fail(PSD_ERR_ARG, "variant must be 0..6");
+    if (variant < 0 || variant > 7) return fail(PSD_ERR_ARG, "variant must be 0..7");
     ctx->variant = variant;
     return PSD_OK;
 }

@@ -5,6 +5,7 @@
 
 #include "poseidon_core.cuh"
 #include "poseidon_tc.cuh"
+#include "poseidon_tc5.cuh"
 
 namespace psd {
 

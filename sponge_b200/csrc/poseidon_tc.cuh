@@ -35,6 +35,7 @@ namespace psd {
 
 constexpr uint32_t kTcFragBytes = 1024;   // one constant: 4 n-tiles x 32 lanes x (b0, b1)
 constexpr uint32_t kTcKBytes = 256;       // one additive constant: 4 n-tiles x 4 column pairs x (k0, k1, k0, k1) s32
+constexpr uint32_t kTc5KBytes = 32;       // layout 1: one additive constant = the eight 32-bit limbs of K 2^32 mod p
 // per-warp shared-memory scratch: two A tiles (32 sponges x 32 bytes, rows padded to 48) and two column-sum
 // exchange tiles (32 sponges x 16 words, rows padded to 20 words); consecutive uses alternate between the two
 // copies so that only the write -> read direction needs a warp barrier
@@ -45,6 +46,7 @@ constexpr uint32_t kTcWarpScratch = 2 * kTcATile + 2 * kTcCTile;   // 8 192 byte
 // Where variant 6 finds its tables (byte offsets into the global image `tab`), see tc_tables.cpp.
 struct TcDesc {
     uint32_t ok;
+    uint32_t layout;      // 0: mma.sync fragment order (variant 6); 1: tcgen05 K-major core-matrix blocks (variant 7)
     uint32_t mat_off;     // [T][T] fragments of the dense matrix ([0][0] doubles as M00)
     uint32_t pre_off;     // [T][T] fragments of M_pre
     uint32_t ident_off;   // fragment of the constant 1

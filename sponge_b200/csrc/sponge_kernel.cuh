@@ -5,6 +5,7 @@
 
 #include "kernels.cuh"
 #include "poseidon_fp52.cuh"
+#include "poseidon_tc5.cuh"
 
 namespace psd {
 
@@ -49,7 +50,7 @@ __device__ __forceinline__ void store_elem(const uint32_t* x, uint32_t* base, in
 // ------------------------------------------------------------------------------------------------
 template <class F, int T, int ALPHA, int VARIANT>
 __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d) {
-    static_assert(VARIANT != 6, "variant 6 is called with its warp context (permute_tc)");
+    static_assert(VARIANT < 6, "variants 6 and 7 are called with their warp / tile context (permute_tc, permute_tc5)");
     if constexpr (VARIANT == 5) {
         permute_fp52<F, T, ALPHA>(st, d);       // the host only selects this kernel when d.fp_ok
     } else if constexpr (T > 5) {
@@ -91,7 +92,7 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #ifndef PSD_TC_BLOCK
 #define PSD_TC_BLOCK 512
 #endif
-#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 5 ? 512 : 448)
+#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 5 || (VARIANT) == 7 ? 512 : 448)
 #define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) >= 5 ? 1 : 2)
 #if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
 #define PSD_POOL_KIND 1
@@ -137,7 +138,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
     // the last, partly filled warp stay alive: they recompute the last sponge and store nothing.
     const uint64_t i_raw = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = i_raw < a.n;
-    if (VARIANT != 6 && !live) return;
+    if (VARIANT < 6 && !live) return;
     const uint64_t i = live ? i_raw : a.n - 1;
 #if PSD_POOL_KIND == 1
     TcWarp tcw;
@@ -157,6 +158,53 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             while (clock64() - t0 < wait) {
             }
         }
+    }
+    // Variant 7: the block is blockDim.x / 128 tiles of 128 sponges.  Shared memory behind the staged constant image:
+    // [mat T*T][pre T*T][ident] tables, then per tile [A slots T+1][table double buffer], then the tiles' mbarriers.
+    Tc5Tile tile;
+    if (VARIANT == 7) {
+        unsigned char* base = reinterpret_cast<unsigned char*>(c_pool) + ((a.pool_words * 4u + 1023u) & ~1023u);
+        const uint32_t n_tiles = blockDim.x >> 7, tl = threadIdx.x >> 7;
+        unsigned char* tiles0 = base + tc5_static_bytes(T);
+        unsigned char* bars = tiles0 + n_tiles * tc5_tile_bytes(T);
+        uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
+        tile.row = threadIdx.x & 127;
+        tile.leader = tile.row == 0;
+        tile.bar_id = 1 + (int)tl;
+        tile.tab = a.tc_tab;
+        tile.a_ptr = tiles0 + tl * tc5_tile_bytes(T);
+        tile.a_u32 = (uint32_t)__cvta_generic_to_shared(tile.a_ptr);
+        tile.tab_u32 = tile.a_u32 + (T + 1) * kTc5ASlot;
+        tile.static_u32 = (uint32_t)__cvta_generic_to_shared(base);
+        tile.mbar_u32[0] = (uint32_t)__cvta_generic_to_shared(bars + tl * 16);
+        tile.mbar_u32[1] = tile.mbar_u32[0] + 8;
+        tile.parity[0] = tile.parity[1] = 0;
+        if (tile.leader) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tile.mbar_u32[0]));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tile.mbar_u32[1]));
+            asm volatile("fence.mbarrier_init.release.cluster;");
+        }
+        // the dense matrices' tables: global -> shared, once per block (mat and, with partial rounds, M_pre; then 1)
+        {
+            const uint4* g = reinterpret_cast<const uint4*>(a.tc_tab);
+            uint4* sdst = reinterpret_cast<uint4*>(base);
+            const uint32_t mat16 = T * T * kTc5Tab / 16;
+            for (uint32_t q = threadIdx.x; q < mat16; q += blockDim.x) {
+                sdst[q] = __ldg(g + a.tc.mat_off / 16 + q);
+                if (a.d.partial) sdst[mat16 + q] = __ldg(g + a.tc.pre_off / 16 + q);
+            }
+            for (uint32_t q = threadIdx.x; q < kTc5Tab / 16; q += blockDim.x) sdst[2 * mat16 + q] = __ldg(g + a.tc.ident_off / 16 + q);
+        }
+        // tensor memory: 128 columns per tile (a power of two >= 32 in all)
+        const uint32_t cols = n_tiles <= 1 ? 128u : n_tiles == 2 ? 256u : 512u;
+        if (threadIdx.x < 32) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"(cols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tile.tmem = *tmem_slot + tl * 128;
     }
 #endif
     {
@@ -286,7 +334,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                         uint32_t e[8];
 #pragma unroll
                         for (int k = 0; k < 8; k++) e[k] = st[l][k];
-                        if (VARIANT == 6 && !live) {
+                        if (VARIANT >= 6 && !live) {
                             // a padding thread of the last warp: nothing to deliver
                         } else if (a.out_bytes != nullptr) {
                             // squeeze_bytes, mod.rs:256-270: first 31 LE bytes of the canonical value
@@ -308,6 +356,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             if (perm) {
 #if PSD_POOL_KIND == 1
                 if constexpr (VARIANT == 6) permute_tc<F, T, ALPHA>(st, d, a.tc, tcw);
+                else if constexpr (VARIANT == 7) permute_tc5<F, T, ALPHA>(st, d, a.tc, tile);
                 else
 #endif
                     permute<F, T, ALPHA, VARIANT>(st, d);
@@ -316,7 +365,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             }
         }
 
-        if (a.state_out != nullptr && (VARIANT != 6 || live)) {
+        if (a.state_out != nullptr && (VARIANT < 6 || live)) {
 #pragma unroll
             for (int l = 0; l < T; l++) {
                 uint32_t e[8];
@@ -327,6 +376,17 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             }
         }
     }
+#if PSD_POOL_KIND == 1
+    if (VARIANT == 7) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const uint32_t n_tiles = blockDim.x >> 7;
+            const uint32_t cols = n_tiles <= 1 ? 128u : n_tiles == 2 ? 256u : 512u;
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tile.tmem - (threadIdx.x >> 7) * 128), "r"(cols));
+        }
+    }
+#endif
     if (bad && a.err && live) atomicOr(a.err, 1);
 }
 

@@ -34,9 +34,16 @@ inline uint8_t byte_of(const Fe& x, int b) { return (uint8_t)(x.v[b / 8] >> (8 *
 
 // fragment block of the constant with Montgomery form c_mont: for n-tile nt, lane L = 4 g + tg:
 //   b0 = Tab[4 tg + 0..3][8 nt + g],  b1 = Tab[16 + 4 tg + 0..3][8 nt + g]      (lowest byte first)
-void push_frag(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[32], const Fe& c_mont) {
+void push_frag(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[32], const Fe& c_mont, uint32_t layout) {
     Fe tab[32];   // tab[k] = c 256^k 2^32 mod p, canonical
     for (int k = 0; k < 32; k++) tab[k] = hf_from_mont(f, hf_mul(f, c_mont, pow_mont[k]));
+    if (layout == 1) {
+        // B[n = column][k] for tcgen05.mma, K-major, no swizzle: 8-row x 16-byte core matrices, rows contiguous
+        for (int kk = 0; kk < 2; kk++)
+            for (int col = 0; col < 32; col++)
+                for (int i = 0; i < 16; i++) img.push_back(byte_of(tab[16 * kk + i], col));
+        return;
+    }
     for (int nt = 0; nt < 4; nt++)
         for (int lane = 0; lane < 32; lane++) {
             const int g = lane >> 2, tg = lane & 3, col = 8 * nt + g;
@@ -48,10 +55,14 @@ void push_frag(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[
 // accumulator start values of the additive constant with Montgomery residue k_mont: bytes of K' = K 2^32 mod p;
 // for n-tile nt and column pair tg four little-endian s32: K'[8 nt + 2 tg], K'[8 nt + 2 tg + 1], and the same
 // pair again (the C operand of mma.m16n8k32 holds two rows of the pair)
-void push_kfrag(std::vector<uint8_t>& img, const HostField& f, const Fe& pow32_mont, const Fe& k_mont) {
+void push_kfrag(std::vector<uint8_t>& img, const HostField& f, const Fe& pow32_mont, const Fe& k_mont, uint32_t layout) {
     // k_mont IS the integer to be added to the state (a residue below p); K' = k_mont * 2^32 mod p as an integer:
     // hf_mul(a, b) = a b / R, so with b = 2^32 R mod p (the Montgomery form of 2^32) the product is a 2^32 mod p.
     const Fe kp = hf_mul(f, k_mont, pow32_mont);
+    if (layout == 1) {
+        for (int b = 0; b < 32; b++) img.push_back(byte_of(kp, b));
+        return;
+    }
     for (int nt = 0; nt < 4; nt++)
         for (int tg = 0; tg < 4; tg++)
             for (int e = 0; e < 4; e++) {
@@ -96,8 +107,9 @@ bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why) {
 }
 
 void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
-                     const std::vector<Fe>& ark, const std::vector<Fe>& mds, TcDesc& td, std::vector<uint8_t>& img) {
+                     const std::vector<Fe>& ark, const std::vector<Fe>& mds, TcDesc& td, std::vector<uint8_t>& img, uint32_t layout) {
     memset(&td, 0, sizeof td);
+    td.layout = layout;
     img.clear();
     const uint32_t half = full_rounds / 2, rp = partial_rounds, n = t - 1, total = full_rounds + rp;
     if (half == 0 || full_rounds - half == 0) return;
@@ -128,24 +140,24 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
     auto here = [&img]() { return (uint32_t)img.size(); };
 
     td.mat_off = here();
-    for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, mds[i]);
+    for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, mds[i], layout);
     if (rp) {
         td.pre_off = here();
-        for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, m_pre[i]);
+        for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, m_pre[i], layout);
     }
     td.ident_off = here();
-    push_frag(img, f, pow_mont, hf_one(f));
+    push_frag(img, f, pow_mont, hf_one(f), layout);
     td.part_off = here();
     for (uint32_t i = 0; i < rp; i++) {
-        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j]);
-        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j]);
+        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j], layout);
+        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j], layout);
     }
     // pairs of partial rounds (an odd count leaves the FIRST round on its own): c_q = sum_j w_j(i+1) v_j(i)
     td.pair_off = here();
     for (uint32_t i = rp & 1; i + 1 < rp; i += 2) {
         Fe c = hf_zero();
         for (uint32_t j = 0; j < n; j++) c = hf_add(f, c, hf_mul(f, w[i + 1][j], v[i][j]));
-        push_frag(img, f, pow_mont, c);
+        push_frag(img, f, pow_mont, c, layout);
     }
     // additive constants in execution order, t per round: what round r's outputs receive is what round r + 1
     // adds before its S-boxes
@@ -160,7 +172,7 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
             else if (!full) k = (j == 0) ? k_lane0[r - half + 1] : zero;
             else if (r + 1 == half && rp) k = (j == 0) ? k_lane0[0] : zero;
             else if (r + 1 < total) k = ark[(size_t)(r + 1) * t + j];
-            push_kfrag(img, f, pow32, k);
+            push_kfrag(img, f, pow32, k, layout);
         }
     }
     while (img.size() % 16) img.push_back(0);
@@ -168,10 +180,14 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
 }
 
 void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const uint8_t* const* frags, const uint8_t* kfrag,
-                 uint32_t* out8) {
-    // column sums, read back from the fragment layout
+                 uint32_t* out8, uint32_t layout) {
+    // column sums, read back from the table layout
     uint64_t col[32];
     for (int c = 0; c < 32; c++) {
+        if (layout == 1) {
+            col[c] = kfrag[c];
+            continue;
+        }
         const int nt = c / 8, tg = (c % 8) / 2, e = c % 2;
         const uint8_t* q = kfrag + ((nt * 4 + tg) * 4 + e) * 4;
         col[c] = (uint64_t)q[0] | ((uint64_t)q[1] << 8) | ((uint64_t)q[2] << 16) | ((uint64_t)q[3] << 24);
@@ -182,7 +198,8 @@ void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const 
             for (int c = 0; c < 32; c++) {
                 const int nt = c / 8, g = c % 8;
                 const int tg = (k % 16) / 4, i = k % 4, hi = k / 16;
-                const uint8_t tb = frags[j][((nt * 32 + (4 * g + tg)) * 2 + hi) * 4 + i];
+                const uint8_t tb = layout == 1 ? frags[j][(k / 16) * 512 + c * 16 + (k % 16)]
+                                               : frags[j][((nt * 32 + (4 * g + tg)) * 2 + hi) * 4 + i];
                 col[c] += (uint64_t)byte * tb;
             }
         }

@@ -11,9 +11,12 @@ namespace psd {
 // constant that multiplies the state, pre-arranged in mma.m16n8k32 B-fragment order, and the additive
 // constants as accumulator start values.  td.ok is set when the variant applies (a factorable matrix, full
 // rounds on both sides of the partial rounds, width <= 5) and the numeric bounds hold.
+// layout 0: every table in mma.sync.m16n8k32 B-fragment order, additive constants as accumulator start values
+// (variant 6).  layout 1: every table as the 32 x 32-byte B operand of tcgen05.mma in the K-major no-swizzle
+// core-matrix order ([k / 16][column][k % 16]), additive constants as eight 32-bit limbs (variant 7).
 void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
                      const std::vector<Fe>& ark_mont, const std::vector<Fe>& mds_mont, TcDesc& td,
-                     std::vector<uint8_t>& img);
+                     std::vector<uint8_t>& img, uint32_t layout = 0);
 
 // The numeric conditions behind variant 6 for a given field and width: column sums below 2^32 / 257, sweep
 // results below 2^256 and inside the S-box's operand range.  *why names the first one that fails.
@@ -23,6 +26,6 @@ bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why);
 // sum_j bytes(x_j) * Tab(c_j) + K' followed by one 32-bit Montgomery row.  x: n_terms values of 8 words
 // (any 256-bit integers), frags / kfrag as laid out by build_tc_tables.
 void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const uint8_t* const* frags, const uint8_t* kfrag,
-                 uint32_t* out8);
+                 uint32_t* out8, uint32_t layout = 0);
 
 }  // namespace psd

@@ -303,6 +303,7 @@ extern "C" int emu_fp52_bounds(int field, uint32_t rate, uint32_t capacity, uint
 
 template <class F, int T, int ALPHA>
 static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf) {
+    const uint32_t kb = td.layout == 1 ? kTc5KBytes : kTcKBytes, lay = td.layout;
     for (int j = 0; j < T; j++) {
         uint32_t c[8];
         cload8(c, d.ark_off + j * 8);
@@ -319,15 +320,15 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
         for (int i = 0; i < T; i++) {
             const uint8_t* frags[T];
             for (int j = 0; j < T; j++) frags[j] = mat + (i * T + j) * kTcFragBytes;
-            tc_host_row(hf, &y[0][0], T, frags, kp + i * kTcKBytes, st[i]);
+            tc_host_row(hf, &y[0][0], T, frags, kp + i * kb, st[i], lay);
         }
-        kp += T * kTcKBytes;
+        kp += T * kb;
     };
     for (uint32_t r = 0; r < half; r++) full_round(tab + ((r + 1 == half && rp) ? td.pre_off : td.mat_off));
     if (rp) {
         const uint8_t* part = tab + td.part_off;
         const uint8_t* pair = tab + td.pair_off;
-        const uint32_t round_k = T * kTcKBytes, round_part = 2 * (T - 1) * kTcFragBytes;
+        const uint32_t round_k = T * kb, round_part = 2 * (T - 1) * kTcFragBytes;
         // one round on its own: row 0, then every lane <- 1 lane + v y
         auto single = [&]() {
             tc_sbox<F, ALPHA>(st[0]);
@@ -340,13 +341,13 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                 frags[j] = part + (j - 1) * kTcFragBytes;
             }
             uint32_t n0[8];
-            tc_host_row(hf, &terms[0][0], T, frags, kp, n0);
+            tc_host_row(hf, &terms[0][0], T, frags, kp, n0, lay);
             for (int j = 1; j < T; j++) {
                 uint32_t two[2][8];
                 memcpy(two[0], st[0], 32);   // y
                 memcpy(two[1], st[j], 32);   // the lane
                 const uint8_t* fr[2] = {part + (T - 1 + j - 1) * kTcFragBytes, tab + td.ident_off};
-                tc_host_row(hf, &two[0][0], 2, fr, kp + j * kTcKBytes, st[j]);
+                tc_host_row(hf, &two[0][0], 2, fr, kp + j * kb, st[j], lay);
             }
             memcpy(st[0], n0, 32);
             kp += round_k;
@@ -368,7 +369,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                     memcpy(terms[j], st[j], 32);
                     frags[j] = part + (j - 1) * kTcFragBytes;
                 }
-                tc_host_row(hf, &terms[0][0], T, frags, kp, x1);
+                tc_host_row(hf, &terms[0][0], T, frags, kp, x1, lay);
             }
             memcpy(y1, x1, 32);
             tc_sbox<F, ALPHA>(y1);
@@ -383,7 +384,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                     memcpy(terms[j + 1], st[j], 32);
                     frags[j + 1] = part + round_part + (j - 1) * kTcFragBytes;
                 }
-                tc_host_row(hf, &terms[0][0], T + 1, frags, kp + round_k, x2);
+                tc_host_row(hf, &terms[0][0], T + 1, frags, kp + round_k, x2, lay);
             }
             for (int j = 1; j < T; j++) {
                 uint32_t three[3][8];
@@ -392,7 +393,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                 memcpy(three[2], st[j], 32);
                 const uint8_t* fr[3] = {part + round_part + (T - 1 + j - 1) * kTcFragBytes, part + (T - 1 + j - 1) * kTcFragBytes,
                                         tab + td.ident_off};
-                tc_host_row(hf, &three[0][0], 3, fr, kp + round_k + j * kTcKBytes, st[j]);
+                tc_host_row(hf, &three[0][0], 3, fr, kp + round_k + j * kb, st[j], lay);
             }
             memcpy(st[0], x2, 32);
             kp += 2 * round_k;
@@ -423,8 +424,14 @@ static int emu_perm_tc_a(uint64_t alpha, const PermDesc& d, const TcDesc& td, co
 }
 
 // returns 0 ok, 1 if variant 6 does not apply to the parameter set, -1 unsupported width
+extern "C" int emu_permute_tc_layout(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, uint64_t alpha,
+                                     const uint64_t* ark_canon, const uint64_t* mds_canon, uint32_t* states, size_t n, uint32_t layout);
 extern "C" int emu_permute_tc(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, uint64_t alpha,
                               const uint64_t* ark_canon, const uint64_t* mds_canon, uint32_t* states, size_t n) {
+    return emu_permute_tc_layout(field, rate, capacity, rf, rp, alpha, ark_canon, mds_canon, states, n, 0);
+}
+extern "C" int emu_permute_tc_layout(int field, uint32_t rate, uint32_t capacity, uint32_t rf, uint32_t rp, uint64_t alpha,
+                                     const uint64_t* ark_canon, const uint64_t* mds_canon, uint32_t* states, size_t n, uint32_t layout) {
     const HostField* hf = host_field(field);
     const uint32_t t = rate + capacity, rounds = rf + rp;
     std::vector<Fe> ark(rounds * t), mds(t * t);
@@ -432,7 +439,7 @@ extern "C" int emu_permute_tc(int field, uint32_t rate, uint32_t capacity, uint3
     for (size_t i = 0; i < mds.size(); i++) mds[i] = hf_to_mont(*hf, reinterpret_cast<const Fe*>(mds_canon)[i]);
     TcDesc td{};
     std::vector<uint8_t> tab;
-    build_tc_tables(*hf, t, rf, rp, ark, mds, td, tab);
+    build_tc_tables(*hf, t, rf, rp, ark, mds, td, tab, layout);
     if (!td.ok) return 1;
     PermDesc d{};
     d.ark_off = 0;

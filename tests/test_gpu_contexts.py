@@ -61,7 +61,7 @@ def test_many_live_parameter_sets(ref, field, rate, rf, rp, alpha):
         orc = COracle(ocfg, field_id(ref, ocfg))
         st = orc.synth(600 * t, seed=0xF1)
         exp = orc.permute_batch(st.copy())
-        for v in (0, 1, 2, 3, 5, 6):
+        for v in (0, 1, 2, 3, 5, 6, 7):
             ctx.set_variant(v)
             assert np.array_equal(ctx.permute_batch(st.copy()), exp), (v, ctx.describe())
     finally:

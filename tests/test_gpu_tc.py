@@ -1,6 +1,6 @@
-"""GPU parity for kernel variant 6 (integer S-box + the whole linear layer on the tensor cores: byte-digit tables,
-mma.sync u8 x u8 -> s32, one 32-bit Montgomery row per output value): bit-exact against the CPU oracle through the
-C ABI, for every parameter shape the variant is built for, batch sizes that leave the last warp partly filled
+"""GPU parity for kernel variants 6 and 7 (integer S-box + the whole linear layer on the tensor cores: byte-digit tables,
+u8 x u8 -> s32, one 32-bit Montgomery row per output value; 6 = mma.sync with register fragments, 7 = tcgen05.mma with
+operands in shared memory and accumulators in TMEM): bit-exact against the CPU oracle through the C ABI, for every parameter shape the variant is built for, batch sizes that leave the last warp partly filled
 (the kernel keeps padding threads alive for the warp-collective instructions), every layout / representation,
 the sponge call sequences and the Merkle driver."""
 import numpy as np
@@ -23,14 +23,22 @@ def make(ref, name):
     return S, oc, COracle(oc, field_id(ref, oc)), cfg.context()
 
 
+def has_variant7(oc):
+    """Variant 7 (tcgen05 / TMEM form of the same contraction) is built for widths up to 4."""
+    return oc.rate + oc.capacity <= 4
+
+
+@pytest.mark.parametrize("variant", [6, 7])
 @pytest.mark.parametrize("name", NAMES)
-def test_tc_permute_matches_oracle(ref, name):
+def test_tc_permute_matches_oracle(ref, name, variant):
     S, oc, orc, ctx = make(ref, name)
     try:
-        ctx.set_variant(6)
-        assert ctx.active_variant() == 6, ctx.describe()
+        if variant == 7 and not has_variant7(oc):
+            pytest.skip("variant 7 is not built for this width")
+        ctx.set_variant(variant)
+        assert ctx.active_variant() == variant, ctx.describe()
         t = oc.rate + oc.capacity
-        for n in (1, 31, 33, 4097, 20000):
+        for n in (1, 31, 33, 127, 129, 4097, 20000, 148 * 512 + 77):
             st = orc.synth(n * t, seed=0x7C0 + n)
             if n >= 33:
                 st[:t] = 0
@@ -54,12 +62,15 @@ def test_tc_permute_matches_oracle(ref, name):
         ctx.close()
 
 
+@pytest.mark.parametrize("variant", [6, 7])
 @pytest.mark.parametrize("name", ["bn254_t3", "bn254_t5", "bls_fixture"])
-def test_tc_sponge_calls_and_merkle(ref, name):
+def test_tc_sponge_calls_and_merkle(ref, name, variant):
     S, oc, orc, ctx = make(ref, name)
     try:
-        ctx.set_variant(6)
-        assert ctx.active_variant() == 6
+        if variant == 7 and not has_variant7(oc):
+            pytest.skip("variant 7 is not built for this width")
+        ctx.set_variant(variant)
+        assert ctx.active_variant() == variant
         for n, n_absorb, n_squeeze in ((700, 5, 3), (45, 1, 1), (1000, 0, 2), (513, 9, 4)):
             x = orc.synth(max(n * n_absorb, 1), seed=0x7C2 + n_absorb)[: n * n_absorb]
             assert np.array_equal(ctx.absorb_squeeze_batch(x, n, n_absorb, n_squeeze),

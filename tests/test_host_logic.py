@@ -393,11 +393,13 @@ def test_tensor_core_variant_host_model(emu, ref, name):
     exp = orc.permute_batch(st.copy())
     ark = to_limbs(v for r in cfg.ark for v in r)
     mds = to_limbs(v for r in cfg.mds for v in r)
-    s = st.copy().view(np.uint32)
-    rc = emu.emu_permute_tc(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
-                            C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), C.c_void_p(s.ctypes.data), C.c_size_t(n))
-    if cfg.alpha not in (5, 17):
-        assert rc == 1
-        return
-    assert rc == 0
-    assert np.array_equal(s.view(np.uint64), exp)
+    for layout in (0, 1):   # mma.sync fragment order (variant 6) and tcgen05 core-matrix blocks (variant 7)
+        s = st.copy().view(np.uint32)
+        rc = emu.emu_permute_tc_layout(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
+                                       C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), C.c_void_p(s.ctypes.data),
+                                       C.c_size_t(n), layout)
+        if cfg.alpha not in (5, 17):
+            assert rc == 1
+            continue
+        assert rc == 0
+        assert np.array_equal(s.view(np.uint64), exp), layout
