@@ -613,6 +613,72 @@ PSD_DEV void mont_sqr(uint32_t* r, const uint32_t* a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Unreduced products (variant 7: the reduction is a product by constants and goes to the tensor cores).
+// Same two sliding accumulators as mont_mul / mont_sqr without the Montgomery steps: after row i the lowest
+// column of the lo-aligned accumulator is limb i of the product.  Both accumulators hold parts of an exact
+// partial sum below 2^(256 + 32 (i + 1)), so no chain carries out.
+// ------------------------------------------------------------------------------------------------
+
+// out[0..15] = a * b   (64 wide multiplies)
+PSD_DEV void mul_wide(uint32_t* out, const uint32_t* a, const uint32_t* b) {
+    uint32_t e[8], o[8];
+    mul4(e, a[0], a[2], a[4], a[6], b[0]);
+    mul4(o, a[1], a[3], a[5], a[7], b[0]);
+    out[0] = e[0];
+#define PSD_WIDE_ROW(I, X, Y)                                  \
+    mad4_slide(X, Y[0], a[1], a[3], a[5], a[7], b[I]);         \
+    mad4(Y, a[0], a[2], a[4], a[6], b[I], X[7]);               \
+    out[I] = Y[0];
+    PSD_WIDE_ROW(1, e, o)
+    PSD_WIDE_ROW(2, o, e)
+    PSD_WIDE_ROW(3, e, o)
+    PSD_WIDE_ROW(4, o, e)
+    PSD_WIDE_ROW(5, e, o)
+    PSD_WIDE_ROW(6, o, e)
+    PSD_WIDE_ROW(7, e, o)
+#undef PSD_WIDE_ROW
+    merge8(out + 8, e, o);   // o[0] (= out[7]) is skipped by merge8
+}
+
+// out[0..15] = a^2, a < 2^255   (36 wide multiplies; the doubled operand as in mont_sqr)
+PSD_DEV void sqr_wide(uint32_t* out, const uint32_t* a) {
+    uint32_t d[8];
+#if !defined(PSD_HOST_EMU)
+#pragma unroll
+    for (int k = 1; k < 8; k++) d[k] = __funnelshift_l(a[k - 1], a[k], 1);
+#else
+    for (int k = 1; k < 8; k++) d[k] = (a[k] << 1) | (a[k - 1] >> 31);
+#endif
+    d[0] = 0;
+    uint32_t e[8], o[8];
+    {
+        const uint32_t d1 = d[1] & 0xfffffffeu;
+        mul4(e, a[0], d[2], d[4], d[6], a[0]);
+        mul4(o, d1, d[3], d[5], d[7], a[0]);
+        out[0] = e[0];
+    }
+    uint32_t v[8];
+#define PSD_SQRW_ROW(I, X, Y)                                                    \
+    {                                                                            \
+        _Pragma("unroll") for (int k = 0; k < 8; k++) v[k] = d[k];               \
+        v[I] = a[I];                                                             \
+        if (I < 7) v[I + 1] = d[I + 1] & 0xfffffffeu;                            \
+        mad4_slide_from<I / 2>(X, Y[0], v[1], v[3], v[5], v[7], a[I]);           \
+        mad4_from<(I + 1) / 2>(Y, v[0], v[2], v[4], v[6], a[I], X[7]);           \
+        out[I] = Y[0];                                                           \
+    }
+    PSD_SQRW_ROW(1, e, o)
+    PSD_SQRW_ROW(2, o, e)
+    PSD_SQRW_ROW(3, e, o)
+    PSD_SQRW_ROW(4, o, e)
+    PSD_SQRW_ROW(5, e, o)
+    PSD_SQRW_ROW(6, o, e)
+    PSD_SQRW_ROW(7, e, o)
+#undef PSD_SQRW_ROW
+    merge8(out + 8, e, o);
+}
+
+// ------------------------------------------------------------------------------------------------
 // Wide-window variants.  For BLS12-381 Fr (p ~ 0.45 * 2^256) the running window of a lazily reduced
 // dot product or of the squaring can exceed 9 limbs, so a tenth limb `top` (column 9) collects the
 // carries out of column 8 and re-enters at the top pair when the window slides.  The result can be

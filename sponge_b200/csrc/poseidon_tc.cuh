@@ -46,13 +46,17 @@ constexpr uint32_t kTcWarpScratch = 2 * kTcATile + 2 * kTcCTile;   // 8 192 byte
 // Where variant 6 finds its tables (byte offsets into the global image `tab`), see tc_tables.cpp.
 struct TcDesc {
     uint32_t ok;
-    uint32_t layout;      // 0: mma.sync fragment order (variant 6); 1: tcgen05 K-major core-matrix blocks (variant 7)
+    uint32_t layout;      // 0: mma.sync fragment order (variant 6); 1: tcgen05 K-major core-matrix blocks, 64-row tables for the unreduced
+                          // S-box values, tables that share an operand stacked along N (variant 7)
     uint32_t mat_off;     // [T][T] fragments of the dense matrix ([0][0] doubles as M00)
     uint32_t pre_off;     // [T][T] fragments of M_pre
     uint32_t ident_off;   // fragment of the constant 1
     uint32_t part_off;    // [partial][2(T-1)] fragments: w_1.., v_1.. per partial round
     uint32_t pair_off;    // [partial / 2] fragments: c_q = sum_j w_j(i+1) v_j(i) for the q-th PAIR of partial rounds (i, i+1)
     uint32_t k_off;       // [rounds][T] additive constants (accumulator start values), execution order
+    // layout 1 only (poseidon_tc5.cuh has the table formats)
+    uint32_t red_off;     // 64-row table of the constant 1: the reduction of an unreduced square
+    uint32_t m00_off;     // 64-row table of M00 on its own
 };
 
 // the lazy S-box of fp256.cuh / poseidon_core.cuh on a value < p + 2^241 (BN254), else the reducing one after one

@@ -1,46 +1,71 @@
 // VARIANT 7: variant 6's contraction (products by round constants as u8 x u8 -> s32 matrix products against byte-digit
 // tables, see poseidon_tc.cuh) on the 5th-generation tensor cores: tcgen05.mma.kind::i8 with both operands in shared
-// memory and the accumulators in TMEM.
+// memory and the accumulators in TMEM -- and, because a Montgomery reduction is itself a product by constants
+// (z mod p = sum_k byte_k(z) (256^k mod p)), every reduction of the S-box as well.
 //
-// Why: with mma.sync every warp issues its own MMAs (56 per partial round, 8.8 issue cycles each), builds A fragments with
-// ldmatrix, loads B fragments, and brings the column sums back to the owning thread through shared memory.  Here a thread
-// block is four TILES of 128 sponges (4 warps each); per tile
-//   * every thread writes the 32 bytes of a value ONCE into the tile's A slot (K-major core-matrix layout: 16-byte chunk c of
-//     row r at c * 2048 + r * 16),
-//   * ONE thread issues the MMAs of a whole step (M = 128 sponges, N = 32 columns, K = 32 bytes per instruction; a step is
-//     3..10 instructions) and commits them to the tile's mbarrier,
+// A thread block is four TILES of 128 sponges (4 warps each).  Per tile
+//   * every thread writes the bytes of a value ONCE into an A slot of the tile (K-major core-matrix layout: 16-byte chunk c
+//     of row r at c * 2048 + r * 16): 32 bytes for a state element, 64 bytes for an UNREDUCED product of two elements;
+//   * ONE thread issues the MMAs of a step (M = 128 sponges, K = 32 bytes per instruction, N = 32 columns per constant; the
+//     constants that multiply the same value are stacked along N, so one instruction pair serves row 0 AND all lanes) and
+//     commits them to the tile's mbarrier; measured on B200: 67 cycles per instruction per SM for every N <= 128, so the
+//     instruction COUNT is what the layout minimises;
 //   * the accumulators live in the tile's 128 TMEM columns, and tcgen05.ld.32x32b hands thread r the 32 column sums of ITS
-//     OWN row -- no exchange, no fragments,
-//   * the round's tables (1 KiB per constant, the B operand as stored by the host) are staged per tile with cp.async into
-//     a double buffer one pair of partial rounds ahead; the dense matrices stay in shared memory for the whole block.
-// The arithmetic -- tables, column sums, carry sweep, one 32-bit Montgomery row, lazy S-box, pairs of partial rounds -- is
-// exactly variant 6's, so the two produce the same intermediate values and the host model of tests/emu covers both.
+//     OWN row -- no exchange, no fragments;
+//   * the sweep (pair-combine, carry add, one 32-bit Montgomery row) turns 32 column sums into a value < p + 2^249.
+// The S-box x^5 is then: square (36 wide multiplies, unreduced) -> tensor-core reduction -> square -> reduction -> product
+// with x (64 wide multiplies, unreduced) -> straight into the linear layer, whose tables carry the extra R^-1.  No
+// Montgomery reduction runs on the integer pipe: 136 wide multiplies per S-box instead of 328, for three more trips
+// through the tensor core per round, which the other warps of the SM hide.
+//
+// Shared memory (behind the staged constant image): [M00 table, ident, reduction table][A slots per tile][U], where U holds
+// the dense matrices (M, M_pre, stacked by column) during the full rounds and the per-tile table staging buffers during the
+// partial rounds; the matrices are re-read from the L2-resident image after the partial rounds.
 #pragma once
 #include "poseidon_tc.cuh"
 
+#ifndef PSD_TC5_SQTC
+#define PSD_TC5_SQTC 1   // 1: the S-box's squarings are reduced on the tensor cores; 0: Montgomery squarings on the integer pipe
+#endif
+
 namespace psd {
 
-constexpr uint32_t kTc5ASlot = 4096;    // one value of a 128-sponge tile: [16-byte chunk 0..1][row 0..127][16 bytes]
-constexpr uint32_t kTc5Tab = 1024;      // one table: [k / 16][column 0..31][k % 16]
+constexpr uint32_t kTc5Tab = 1024;      // one 32-row table: [k / 16][column 0..31][k % 16]
+constexpr uint32_t kTc5Chunk = 2048;    // one 16-byte K chunk of an A operand: [row 0..127][16 bytes]
+constexpr uint32_t kTc5Narrow = 4096;   // A slot of a 32-byte value
+constexpr uint32_t kTc5Wide = 8192;     // A slot of a 64-byte value
 constexpr uint32_t kTc5TileRows = 128;
 
-// shared-memory bytes of the variant-7 kernel behind the staged constant image, for T lanes and 4 tiles
 #if defined(__CUDACC__)
 #define PSD_HD __host__ __device__
 #else
 #define PSD_HD
 #endif
-PSD_HD constexpr uint32_t tc5_static_bytes(uint32_t t) { return (2 * t * t + 1) * kTc5Tab; }
-PSD_HD constexpr uint32_t tc5_pair_tables(uint32_t t) { return 4 * (t - 1) + 1; }
-PSD_HD constexpr uint32_t tc5_tile_bytes(uint32_t t) { return (t + 1) * kTc5ASlot + 2 * tc5_pair_tables(t) * kTc5Tab; }
-PSD_HD constexpr uint32_t tc5_smem_bytes(uint32_t t, uint32_t tiles) { return tc5_static_bytes(t) + tiles * tc5_tile_bytes(t) + 128; }
+// block-wide small tables: M00 (64 rows) at 0, ident (32 rows) at 2 KiB, the reduction table (64 rows) at 3 KiB
+PSD_HD constexpr uint32_t tc5_small_bytes() { return 5 * 1024; }
+// A slots of a tile: full rounds T wide slots; partial rounds y0, y1 wide and T - 1 narrow lanes
+PSD_HD constexpr uint32_t tc5_a_bytes(uint32_t t) {
+    return t * kTc5Wide > 2 * kTc5Wide + (t - 1) * kTc5Narrow ? t * kTc5Wide : 2 * kTc5Wide + (t - 1) * kTc5Narrow;
+}
+// staging of a tile for one pair of partial rounds: w(i) [t-1], the stack (c_q, v(i)) [2t], w(i+1) [t-1], the stack
+// (M00, v(i+1)) [2t] KiB
+PSD_HD constexpr uint32_t tc5_stage_bytes(uint32_t t) { return (6 * t - 2) * 1024; }
+PSD_HD constexpr uint32_t tc5_u_bytes(uint32_t t, uint32_t tiles) {
+    return 4 * t * t * 1024 > tiles * tc5_stage_bytes(t) ? 4 * t * t * 1024 : tiles * tc5_stage_bytes(t);
+}
+PSD_HD constexpr uint32_t tc5_smem_bytes(uint32_t t, uint32_t tiles) {
+    return tc5_small_bytes() + tiles * tc5_a_bytes(t) + tc5_u_bytes(t, tiles) + 128;
+}
 
 #if defined(__CUDACC__)
 
 struct Tc5Tile {
     uint32_t tmem;            // TMEM address of this tile's column 0 (lane field 0)
-    uint32_t a_u32, tab_u32;  // shared-memory addresses of the tile's A slots / table double buffer
-    uint32_t static_u32;      // ... of the block's static tables: mat [T*T], pre [T*T], ident
+    uint32_t a_u32;           // shared-memory address of the tile's A slots
+    uint32_t stage_u32;       // ... of the tile's staging buffer (inside U)
+    uint32_t small_u32;       // ... of the block's small tables
+    uint32_t u_u32;           // ... of U
+    uint32_t u_bytes;         // matrices to restore into U after the partial rounds
     // Two mbarriers per tile: a step commits twice (row 0 first, the lanes behind it), and a waiter may be at most one
     // phase behind an mbarrier, so the two completions must not share one.
     uint32_t mbar_u32[2];
@@ -56,24 +81,34 @@ __device__ __forceinline__ uint64_t tc5_desc(uint32_t saddr, uint32_t lbo) {
     // K-major, no swizzle, version 1; 8-row groups 128 bytes apart; lbo = bytes between the two 16-byte K chunks
     return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
 }
-constexpr uint32_t kTc5Idesc = (2u << 4) | ((32u >> 3) << 17) | ((128u >> 4) << 24);   // u8 x u8 -> s32, M 128, N 32
+// u8 x u8 -> s32, M 128, N n
+__device__ __forceinline__ constexpr uint32_t tc5_idesc(uint32_t n) { return (2u << 4) | ((n >> 3) << 17) | ((128u >> 4) << 24); }
 
-// D[tile columns d_col .. +31] (+)= A(slot) x Tab(b_u32)^T
-__device__ __forceinline__ void tc5_mma(const Tc5Tile& t, uint32_t a_slot, uint32_t b_u32, uint32_t d_col, bool accumulate) {
-    const uint64_t da = tc5_desc(t.a_u32 + a_slot * kTc5ASlot, 2048), db = tc5_desc(b_u32, 512);
+// D[columns d .. d + 32 blocks - 1] (+)= A (128 rows x 32 bytes at a_u32) x B^T (32 blocks columns x 32 bytes at b_u32)
+__device__ __forceinline__ void tc5_mma(uint32_t d, uint32_t a_u32, uint32_t b_u32, uint32_t blocks, bool accumulate) {
+    const uint64_t da = tc5_desc(a_u32, kTc5Chunk), db = tc5_desc(b_u32, blocks * 512);
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
-                 ::"r"(t.tmem + d_col), "l"(da), "l"(db), "r"(kTc5Idesc), "r"((uint32_t)accumulate), "r"(0u) : "memory");
+                 ::"r"(d), "l"(da), "l"(db), "r"(tc5_idesc(32 * blocks)), "r"((uint32_t)accumulate), "r"(0u) : "memory");
+}
+// a 64-byte value against a stack of `blocks` 64-row tables: two instructions
+__device__ __forceinline__ void tc5_mma_wide(uint32_t d, uint32_t a_u32, uint32_t b_u32, uint32_t blocks, bool accumulate) {
+    tc5_mma(d, a_u32, b_u32, blocks, accumulate);
+    tc5_mma(d, a_u32 + 2 * kTc5Chunk, b_u32 + 2 * blocks * 512, blocks, true);
 }
 __device__ __forceinline__ void tc5_commit(const Tc5Tile& t, int which) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(t.mbar_u32[which]) : "memory");
 }
 
-// this thread's 32 bytes of a value -> A slot
-__device__ __forceinline__ void tc5_store_a(const Tc5Tile& t, uint32_t slot, const uint32_t* x) {
-    unsigned char* p = t.a_ptr + slot * kTc5ASlot + t.row * 16;
+// this thread's bytes of a value -> A slot at byte offset `off` of the tile's A region
+__device__ __forceinline__ void tc5_store_a(const Tc5Tile& t, uint32_t off, const uint32_t* x) {
+    unsigned char* p = t.a_ptr + off + t.row * 16;
     *reinterpret_cast<uint4*>(p) = make_uint4(x[0], x[1], x[2], x[3]);
-    *reinterpret_cast<uint4*>(p + 2048) = make_uint4(x[4], x[5], x[6], x[7]);
+    *reinterpret_cast<uint4*>(p + kTc5Chunk) = make_uint4(x[4], x[5], x[6], x[7]);
+}
+__device__ __forceinline__ void tc5_store_wide(const Tc5Tile& t, uint32_t off, const uint32_t* x) {
+    tc5_store_a(t, off, x);
+    tc5_store_a(t, off + 2 * kTc5Chunk, x + 8);
 }
 
 // All 128 threads of the tile: what they wrote to shared memory (A slots, staged tables) becomes visible to the tensor
@@ -111,10 +146,10 @@ __device__ __forceinline__ void tc5_load(const Tc5Tile& t, uint32_t d_col, int (
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// 32 column sums (+ the additive constant K 2^32 mod p, eight limbs at kptr) -> 8 limbs, value < p + 2^241:
+// 32 column sums (+ the additive constant K 2^32 mod p, eight limbs at kptr, if HASK) -> 8 limbs, value < p + 2^249:
 // columns 4l, 4l+1 and 4l+2, 4l+3 pair up (sum < 2^32 / 257), the pairs form two 256-bit numbers X + (Y << 16), then one
 // 32-bit Montgomery row -- the same sweep as variant 6, minus its exchange through shared memory
-template <class F>
+template <class F, bool HASK>
 __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], const unsigned char* kptr) {
     uint32_t X[8], Y[8];
 #pragma unroll
@@ -127,7 +162,6 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
 #pragma unroll
     for (int k = 1; k < 8; k++) ys[k] = __funnelshift_l(Y[k - 1], Y[k], 16);
     ys[8] = Y[7] >> 16;
-    const uint4 k0 = __ldg(reinterpret_cast<const uint4*>(kptr)), k1 = __ldg(reinterpret_cast<const uint4*>(kptr) + 1);
     uint32_t v[9];
     asm("add.cc.u32 %0, %9, %18;\n\t"
         "addc.cc.u32 %1, %10, %19;\n\t"
@@ -141,17 +175,20 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8])
         : "r"(X[0]), "r"(X[1]), "r"(X[2]), "r"(X[3]), "r"(X[4]), "r"(X[5]), "r"(X[6]), "r"(X[7]), "r"(ys[8]), "r"(ys[0]),
           "r"(ys[1]), "r"(ys[2]), "r"(ys[3]), "r"(ys[4]), "r"(ys[5]), "r"(ys[6]), "r"(ys[7]));
-    asm("add.cc.u32 %0, %0, %9;\n\t"
-        "addc.cc.u32 %1, %1, %10;\n\t"
-        "addc.cc.u32 %2, %2, %11;\n\t"
-        "addc.cc.u32 %3, %3, %12;\n\t"
-        "addc.cc.u32 %4, %4, %13;\n\t"
-        "addc.cc.u32 %5, %5, %14;\n\t"
-        "addc.cc.u32 %6, %6, %15;\n\t"
-        "addc.cc.u32 %7, %7, %16;\n\t"
-        "addc.u32 %8, %8, 0;"
-        : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8])
-        : "r"(k0.x), "r"(k0.y), "r"(k0.z), "r"(k0.w), "r"(k1.x), "r"(k1.y), "r"(k1.z), "r"(k1.w));
+    if (HASK) {
+        const uint4 k0 = __ldg(reinterpret_cast<const uint4*>(kptr)), k1 = __ldg(reinterpret_cast<const uint4*>(kptr) + 1);
+        asm("add.cc.u32 %0, %0, %9;\n\t"
+            "addc.cc.u32 %1, %1, %10;\n\t"
+            "addc.cc.u32 %2, %2, %11;\n\t"
+            "addc.cc.u32 %3, %3, %12;\n\t"
+            "addc.cc.u32 %4, %4, %13;\n\t"
+            "addc.cc.u32 %5, %5, %14;\n\t"
+            "addc.cc.u32 %6, %6, %15;\n\t"
+            "addc.cc.u32 %7, %7, %16;\n\t"
+            "addc.u32 %8, %8, 0;"
+            : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8])
+            : "r"(k0.x), "r"(k0.y), "r"(k0.z), "r"(k0.w), "r"(k1.x), "r"(k1.y), "r"(k1.z), "r"(k1.w));
+    }
     const uint32_t m = v[0] * np0<F>();
     uint32_t c8 = 0;
     mad4(v, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, c8);
@@ -161,32 +198,131 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
     for (int k = 0; k < 8; k++) out[k] = x[k];
 }
 
-// n_kb KiB of tables, global -> the tile's staging buffer `buf` at KiB position `at`, by cp.async (no registers held)
-__device__ __forceinline__ void tc5_stage(const Tc5Tile& t, uint32_t buf_u32, uint32_t at, const unsigned char* src, uint32_t n_kb) {
-    for (uint32_t q = t.row; q < n_kb * 64; q += kTc5TileRows) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(buf_u32 + at * kTc5Tab + q * 16), "l"(src + q * 16) : "memory");
+// `bytes` of tables, global -> shared at dst_u32, by cp.async (no registers held), spread over the tile's threads
+__device__ __forceinline__ void tc5_stage(const Tc5Tile& t, uint32_t dst_u32, const unsigned char* src, uint32_t bytes) {
+    for (uint32_t q = t.row; q < bytes / 16; q += kTc5TileRows) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_u32 + q * 16), "l"(src + q * 16) : "memory");
     }
 }
-__device__ __forceinline__ void tc5_stage_wait() {
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
+__device__ __forceinline__ void tc5_stage_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tc5_stage_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// The dense matrices' stacks, image -> U, by the whole block; ends with everything visible to the tensor core.
+template <int T>
+__device__ __forceinline__ void tc5_load_matrices(const Tc5Tile& t, const TcDesc& td, bool with_pre) {
+    constexpr uint32_t kMat = 2 * T * T * 1024;
+    for (uint32_t q = threadIdx.x; q < kMat / 16; q += blockDim.x) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + q * 16), "l"(t.tab + td.mat_off + q * 16) : "memory");
+        if (with_pre)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + kMat + q * 16), "l"(t.tab + td.pre_off + q * 16) : "memory");
+    }
+    tc5_stage_commit();
+    tc5_stage_wait();
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
 }
 
-// One full round: T S-boxes into A slots 0..T-1, T x T instructions, T sweeps.  mat_u32: the dense matrix's tables in shared
-// memory ([row i][column j]), kp: the T additive constants of the round.
+// y (8 limbs, < 2^255) <- (w mod p) R^-1-adjusted, w = the 64-byte value just stored at slot `off`: one trip through the
+// tensor core against the reduction table, result in tile column block 0
+template <class F>
+__device__ __forceinline__ void tc5_reduce(uint32_t* y, uint32_t off, uint32_t d_col, Tc5Tile& t) {
+    tc5_step_begin(t);
+    if (t.leader) {
+        tc5_mma_wide(t.tmem + d_col, t.a_u32 + off, t.small_u32 + 3 * 1024, 1, false);
+        tc5_commit(t, 0);
+    }
+    tc5_wait(t, 0);
+    int c[32];
+    tc5_load(t, d_col, c);
+    tc5_sweep<F, false>(y, c, nullptr);
+}
+
+// x^(ALPHA - 1) of a sweep result, by the integer pipe alone (PSD_TC5_SQTC == 0): the lazy squarings of tc_sbox
+template <class F, int ALPHA>
+__device__ __forceinline__ void tc5_pow_int(uint32_t* y, uint32_t* in, const uint32_t* x) {
+    constexpr bool kLazy = (F::kBits == 254);
+    if (kLazy) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) in[k] = x[k];
+    } else {
+        cond_sub_p<F>(in, x);
+    }
+    fp_sqr<F, !kLazy>(y, in);
+#pragma unroll
+    for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, !kLazy>(y, y);
+}
+
+// the S-box of ONE value: x -> the unreduced 64 bytes of x^ALPHA in the wide slot at `off`
+template <class F, int ALPHA>
+__device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, Tc5Tile& t) {
+    uint32_t y[8], in[8], w[16];
+#if PSD_TC5_SQTC
+#pragma unroll
+    for (int k = 0; k < 8; k++) in[k] = y[k] = x[k];
+#pragma unroll
+    for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) {
+        sqr_wide(w, y);
+        tc5_store_wide(t, off, w);
+        tc5_reduce<F>(y, off, 0, t);
+    }
+#else
+    tc5_pow_int<F, ALPHA>(y, in, x);
+#endif
+    mul_wide(w, y, in);
+    tc5_store_wide(t, off, w);
+}
+
+// One full round: T S-boxes into the wide slots 0..T-1, 2 T instructions (S-box output j against column j of the matrix,
+// all rows stacked), T sweeps.  mat_u32: the matrix's stacks in U, kp: the T additive constants of the round.
 template <class F, int T, int ALPHA>
 __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t mat_u32, const unsigned char* kp, Tc5Tile& t) {
+    uint32_t y[T][8];
+#if PSD_TC5_SQTC
+#pragma unroll
+    for (int j = 0; j < T; j++)
+#pragma unroll
+        for (int k = 0; k < 8; k++) y[j][k] = st[j][k];
+#pragma unroll
+    for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) {
+#pragma unroll
+        for (int j = 0; j < T; j++) {
+            uint32_t w[16];
+            sqr_wide(w, y[j]);
+            tc5_store_wide(t, j * kTc5Wide, w);
+        }
+        tc5_step_begin(t);
+        if (t.leader) {
+#pragma unroll
+            for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem + 32 * j, t.a_u32 + j * kTc5Wide, t.small_u32 + 3 * 1024, 1, false);
+            tc5_commit(t, 0);
+        }
+        tc5_wait(t, 0);
+#pragma unroll
+        for (int j = 0; j < T; j++) {
+            int c[32];
+            tc5_load(t, 32 * j, c);
+            tc5_sweep<F, false>(y[j], c, nullptr);
+        }
+    }
+#else
 #pragma unroll
     for (int j = 0; j < T; j++) {
-        tc_sbox<F, ALPHA>(st[j]);
-        tc5_store_a(t, j, st[j]);
+        uint32_t in[8];
+        tc5_pow_int<F, ALPHA>(y[j], in, st[j]);
+#pragma unroll
+        for (int k = 0; k < 8; k++) st[j][k] = in[k];
+    }
+#endif
+#pragma unroll
+    for (int j = 0; j < T; j++) {
+        uint32_t w[16];
+        mul_wide(w, y[j], st[j]);
+        tc5_store_wide(t, j * kTc5Wide, w);
     }
     tc5_step_begin(t);
     if (t.leader) {
 #pragma unroll
-        for (int i = 0; i < T; i++)
-#pragma unroll
-            for (int j = 0; j < T; j++) tc5_mma(t, j, mat_u32 + (i * T + j) * kTc5Tab, 32 * i, j > 0);
+        for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem, t.a_u32 + j * kTc5Wide, mat_u32 + j * 2 * T * 1024, T, j > 0);
         tc5_commit(t, 0);
     }
     tc5_wait(t, 0);
@@ -194,16 +330,20 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
     for (int i = 0; i < T; i++) {
         int c[32];
         tc5_load(t, 32 * i, c);
-        tc5_sweep<F>(st[i], c, kp + i * kTc5KBytes);
+        tc5_sweep<F, true>(st[i], c, kp + i * kTc5KBytes);
     }
 }
 
 template <class F, int T, int ALPHA>
 __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, Tc5Tile& t) {
     static_assert(ALPHA == 5 || ALPHA == 17, "variant 7: alpha 5 or 17");
-    static_assert(T <= 4, "variant 7: a tile's 128 TMEM columns hold T <= 4 output values");
-    constexpr uint32_t kRoundK = T * kTc5KBytes, kRoundPart = 2 * (T - 1) * kTc5Tab, kPairTabs = tc5_pair_tables(T);
-    // A slots: 0 = y0, 1 = y1, 2.. = lanes 1..T-1 (full rounds use 0..T-1)
+    static_assert(T >= 2 && T <= 4, "variant 7: a tile's 128 TMEM columns hold T <= 4 output values");
+    constexpr uint32_t N = T - 1, kRoundK = T * kTc5KBytes, kStack = 2 * T * 1024, kRoundPart = N * kTc5Tab + kStack;
+    // A slots of the partial rounds
+    constexpr uint32_t kY0 = 0, kY1 = kTc5Wide, kLane = 2 * kTc5Wide;
+    // staging: w(i), the stack (c_q, v(i)), then -- one contiguous piece of the image -- w(i+1) and the stack (M00, v(i+1))
+    const uint32_t sWa = t.stage_u32, sBy0 = sWa + N * kTc5Tab, sWb = sBy0 + kStack, sBy1 = sWb + N * kTc5Tab;
+    const uint32_t m00_u32 = t.small_u32, ident_u32 = t.small_u32 + 2 * 1024;
 #pragma unroll
     for (int j = 0; j < T; j++) {
         uint32_t c[8];
@@ -212,7 +352,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
     }
     const uint32_t half = d.half_full, rp = d.partial;
     const unsigned char* kp = t.tab + td.k_off;
-    const uint32_t mat_u32 = t.static_u32, pre_u32 = t.static_u32 + T * T * kTc5Tab, ident_u32 = t.static_u32 + 2 * T * T * kTc5Tab;
+    const uint32_t mat_u32 = t.u_u32, pre_u32 = t.u_u32 + T * kStack;
 
 #pragma unroll 1
     for (uint32_t r = 0; r < half; r++) {
@@ -224,129 +364,124 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
         const unsigned char* part = t.tab + td.part_off;
         const unsigned char* pair = t.tab + td.pair_off;
         const uint32_t pairs = rp >> 1;
-        uint32_t buf = 0;   // staging buffer in use
-        // lanes into their slots; the first round's (or pair's) tables
-#pragma unroll
-        for (int j = 1; j < T; j++) tc5_store_a(t, 1 + j, st[j]);
+        // every tile has seen its last full round complete: U turns into the staging buffers
+        __syncthreads();
         if (rp & 1) {
-            tc5_stage(t, t.tab_u32, 0, part, 2 * (T - 1));
+            tc5_stage(t, sWb, part, kRoundPart);
         } else {
-            tc5_stage(t, t.tab_u32, 0, part, 4 * (T - 1));
-            tc5_stage(t, t.tab_u32, 4 * (T - 1), pair, 1);
+            tc5_stage(t, sWa, part, N * kTc5Tab);
+            tc5_stage(t, sBy0, pair, kStack);
+            tc5_stage(t, sWb, part + kRoundPart, kRoundPart);
         }
-        tc_sbox<F, ALPHA>(st[0]);
-        tc5_store_a(t, 0, st[0]);
-        tc5_stage_wait();
+        tc5_stage_commit();
+#pragma unroll
+        for (int j = 1; j < T; j++) tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
         if (rp & 1) {
-            // an odd number of partial rounds: the first one on its own.  tables: w_1.. at 0, v_1.. at T-1
-            const uint32_t tb = t.tab_u32;
-            if (pairs) {   // the first pair's tables go to the other buffer meanwhile
-                tc5_stage(t, t.tab_u32 + kPairTabs * kTc5Tab, 0, part + kRoundPart, 4 * (T - 1));
-                tc5_stage(t, t.tab_u32 + kPairTabs * kTc5Tab, 4 * (T - 1), pair, 1);
-            }
+            // an odd number of partial rounds: the first one on its own.  y0 against the stack (M00, v): row 0 and lanes
+            tc5_sbox_slot<F, ALPHA>(st[0], kY0, t);
+            tc5_stage_wait();
             tc5_step_begin(t);
             if (t.leader) {
-                tc5_mma(t, 0, mat_u32, 0, false);
+                tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy1, T, false);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t, 1 + j, tb + (j - 1) * kTc5Tab, 0, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWb + (j - 1) * kTc5Tab, 1, true);
                 tc5_commit(t, 0);
 #pragma unroll
-                for (int j = 1; j < T; j++) {
-                    tc5_mma(t, 0, tb + (T - 1 + j - 1) * kTc5Tab, 32 * j, false);
-                    tc5_mma(t, 1 + j, ident_u32, 32 * j, true);
-                }
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, t.a_u32 + kLane + (j - 1) * kTc5Narrow, ident_u32, 1, true);
                 tc5_commit(t, 1);
             }
             tc5_wait(t, 0);
             {
                 int c[32];
                 tc5_load(t, 0, c);
-                tc5_sweep<F>(st[0], c, kp);
+                tc5_sweep<F, true>(st[0], c, kp);
             }
-            if (pairs) tc_sbox<F, ALPHA>(st[0]);
             tc5_wait(t, 1);
 #pragma unroll
             for (int j = 1; j < T; j++) {
                 int c[32];
                 tc5_load(t, 32 * j, c);
-                tc5_sweep<F>(st[j], c, kp + j * kTc5KBytes);
-                if (pairs) tc5_store_a(t, 1 + j, st[j]);
-            }
-            if (pairs) {
-                tc5_store_a(t, 0, st[0]);
-                tc5_stage_wait();
+                tc5_sweep<F, true>(st[j], c, kp + j * kTc5KBytes);
+                if (pairs) tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
             }
             kp += kRoundK;
             part += kRoundPart;
-            buf = 1;
+            if (pairs) {
+                tc5_stage(t, sWa, part, N * kTc5Tab);
+                tc5_stage(t, sBy0, pair, kStack);
+                tc5_stage(t, sWb, part + kRoundPart, kRoundPart);
+                tc5_stage_commit();
+            }
         }
 #pragma unroll 1
         for (uint32_t q = 0; q < pairs; q++) {
             const bool last = q + 1 == pairs;
-            // tables of this pair: w(i) at 0, v(i) at T-1, w(i+1) at 2(T-1), v(i+1) at 3(T-1), c_q at 4(T-1)
-            const uint32_t tb = t.tab_u32 + buf * kPairTabs * kTc5Tab;
-            // first row 0:  M00 y0 + sum_j w_j(i) s_j
+            // first round of the pair:  row 0 = M00 y0 + sum_j w_j(i) s_j
+            tc5_sbox_slot<F, ALPHA>(st[0], kY0, t);
+            tc5_stage_wait();
             tc5_step_begin(t);
             if (t.leader) {
-                tc5_mma(t, 0, mat_u32, 0, false);
+                tc5_mma_wide(t.tmem, t.a_u32 + kY0, m00_u32, 1, false);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t, 1 + j, tb + (j - 1) * kTc5Tab, 0, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWa + (j - 1) * kTc5Tab, 1, true);
                 tc5_commit(t, 0);
-            }
-            // the next pair's tables start their way into the other buffer (its last readers finished a pair ago)
-            if (!last) {
-                tc5_stage(t, t.tab_u32 + (buf ^ 1) * kPairTabs * kTc5Tab, 0, part + 2 * kRoundPart, 4 * (T - 1));
-                tc5_stage(t, t.tab_u32 + (buf ^ 1) * kPairTabs * kTc5Tab, 4 * (T - 1), pair + kTc5Tab, 1);
             }
             tc5_wait(t, 0);
             {
                 int c[32];
                 tc5_load(t, 0, c);
-                tc5_sweep<F>(st[0], c, kp);
+                tc5_sweep<F, true>(st[0], c, kp);
             }
-            tc_sbox<F, ALPHA>(st[0]);
-            tc5_store_a(t, 1, st[0]);
-            // second row 0:  M00 y1 + c_q y0 + sum_j w_j(i+1) s_j ; then the lanes:  1 s_j + v_j(i) y0 + v_j(i+1) y1
+            // second round:  y1 (M00, v(i+1)) + y0 (c_q, v(i)) fill row 0 and the lanes' columns at once; the lanes add
+            // w_j(i+1) s_j to row 0 and 1 s_j to their own columns
+            tc5_sbox_slot<F, ALPHA>(st[0], kY1, t);
             tc5_step_begin(t);
             if (t.leader) {
-                tc5_mma(t, 1, mat_u32, 0, false);
-                tc5_mma(t, 0, tb + 4 * (T - 1) * kTc5Tab, 0, true);
+                tc5_mma_wide(t.tmem, t.a_u32 + kY1, sBy1, T, false);
+                tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy0, T, true);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t, 1 + j, tb + (2 * (T - 1) + j - 1) * kTc5Tab, 0, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWb + (j - 1) * kTc5Tab, 1, true);
                 tc5_commit(t, 0);
 #pragma unroll
-                for (int j = 1; j < T; j++) {
-                    tc5_mma(t, 1, tb + (3 * (T - 1) + j - 1) * kTc5Tab, 32 * j, false);
-                    tc5_mma(t, 0, tb + (T - 1 + j - 1) * kTc5Tab, 32 * j, true);
-                    tc5_mma(t, 1 + j, ident_u32, 32 * j, true);
-                }
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, t.a_u32 + kLane + (j - 1) * kTc5Narrow, ident_u32, 1, true);
                 tc5_commit(t, 1);
             }
             tc5_wait(t, 0);
             {
                 int c[32];
                 tc5_load(t, 0, c);
-                tc5_sweep<F>(st[0], c, kp + kRoundK);
+                tc5_sweep<F, true>(st[0], c, kp + kRoundK);
             }
-            // independent of each other: the S-box of the next pair's first round and this pair's lane sweeps
-            if (!last) tc_sbox<F, ALPHA>(st[0]);
             tc5_wait(t, 1);
+            if (last) {
+                // the last partial round's lanes receive the constants moved behind the partial rounds
 #pragma unroll
-            for (int j = 1; j < T; j++) {
-                int c[32];
-                tc5_load(t, 32 * j, c);
-                tc5_sweep<F>(st[j], c, kp + kRoundK + j * kTc5KBytes);
-                if (!last) tc5_store_a(t, 1 + j, st[j]);
-            }
-            if (!last) {
-                tc5_store_a(t, 0, st[0]);
-                tc5_stage_wait();
+                for (int j = 1; j < T; j++) {
+                    int c[32];
+                    tc5_load(t, 32 * j, c);
+                    tc5_sweep<F, true>(st[j], c, kp + kRoundK + j * kTc5KBytes);
+                }
+            } else {
+#pragma unroll
+                for (int j = 1; j < T; j++) {
+                    int c[32];
+                    tc5_load(t, 32 * j, c);
+                    tc5_sweep<F, false>(st[j], c, nullptr);
+                    tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
+                }
+                // every instruction that read the staging buffers has completed: the next pair's tables
+                tc5_stage(t, sWa, part + 2 * kRoundPart, N * kTc5Tab);
+                tc5_stage(t, sBy0, pair + kStack, kStack);
+                tc5_stage(t, sWb, part + 3 * kRoundPart, kRoundPart);
+                tc5_stage_commit();
             }
             kp += 2 * kRoundK;
             part += 2 * kRoundPart;
-            pair += kTc5Tab;
-            buf ^= 1;
+            pair += kStack;
         }
+        // all tiles are through with the staging buffers: the matrices return to U
+        __syncthreads();
+        tc5_load_matrices<T>(t, td, true);
     }
 
 #pragma unroll 1

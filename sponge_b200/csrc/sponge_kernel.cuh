@@ -160,22 +160,25 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         }
     }
     // Variant 7: the block is blockDim.x / 128 tiles of 128 sponges.  Shared memory behind the staged constant image:
-    // [mat T*T][pre T*T][ident] tables, then per tile [A slots T+1][table double buffer], then the tiles' mbarriers.
+    // [M00, ident, reduction tables][A slots per tile][U: matrices / per-tile staging], then the tiles' mbarriers
+    // (poseidon_tc5.cuh).
     Tc5Tile tile;
     if (VARIANT == 7) {
         unsigned char* base = reinterpret_cast<unsigned char*>(c_pool) + ((a.pool_words * 4u + 1023u) & ~1023u);
         const uint32_t n_tiles = blockDim.x >> 7, tl = threadIdx.x >> 7;
-        unsigned char* tiles0 = base + tc5_static_bytes(T);
-        unsigned char* bars = tiles0 + n_tiles * tc5_tile_bytes(T);
+        unsigned char* a0 = base + tc5_small_bytes();
+        unsigned char* u0 = a0 + n_tiles * tc5_a_bytes(T);
+        unsigned char* bars = u0 + tc5_u_bytes(T, n_tiles);
         uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
         tile.row = threadIdx.x & 127;
         tile.leader = tile.row == 0;
         tile.bar_id = 1 + (int)tl;
         tile.tab = a.tc_tab;
-        tile.a_ptr = tiles0 + tl * tc5_tile_bytes(T);
+        tile.a_ptr = a0 + tl * tc5_a_bytes(T);
         tile.a_u32 = (uint32_t)__cvta_generic_to_shared(tile.a_ptr);
-        tile.tab_u32 = tile.a_u32 + (T + 1) * kTc5ASlot;
-        tile.static_u32 = (uint32_t)__cvta_generic_to_shared(base);
+        tile.small_u32 = (uint32_t)__cvta_generic_to_shared(base);
+        tile.u_u32 = (uint32_t)__cvta_generic_to_shared(u0);
+        tile.stage_u32 = tile.u_u32 + tl * tc5_stage_bytes(T);
         tile.mbar_u32[0] = (uint32_t)__cvta_generic_to_shared(bars + tl * 16);
         tile.mbar_u32[1] = tile.mbar_u32[0] + 8;
         tile.parity[0] = tile.parity[1] = 0;
@@ -184,16 +187,13 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tile.mbar_u32[1]));
             asm volatile("fence.mbarrier_init.release.cluster;");
         }
-        // the dense matrices' tables: global -> shared, once per block (mat and, with partial rounds, M_pre; then 1)
+        // the block's small tables: M00 (2 KiB), ident (1 KiB), the reduction table (2 KiB)
         {
             const uint4* g = reinterpret_cast<const uint4*>(a.tc_tab);
             uint4* sdst = reinterpret_cast<uint4*>(base);
-            const uint32_t mat16 = T * T * kTc5Tab / 16;
-            for (uint32_t q = threadIdx.x; q < mat16; q += blockDim.x) {
-                sdst[q] = __ldg(g + a.tc.mat_off / 16 + q);
-                if (a.d.partial) sdst[mat16 + q] = __ldg(g + a.tc.pre_off / 16 + q);
-            }
-            for (uint32_t q = threadIdx.x; q < kTc5Tab / 16; q += blockDim.x) sdst[2 * mat16 + q] = __ldg(g + a.tc.ident_off / 16 + q);
+            for (uint32_t q = threadIdx.x; q < 128; q += blockDim.x) sdst[q] = __ldg(g + a.tc.m00_off / 16 + q);
+            for (uint32_t q = threadIdx.x; q < 64; q += blockDim.x) sdst[128 + q] = __ldg(g + a.tc.ident_off / 16 + q);
+            for (uint32_t q = threadIdx.x; q < 128; q += blockDim.x) sdst[192 + q] = __ldg(g + a.tc.red_off / 16 + q);
         }
         // tensor memory: 128 columns per tile (a power of two >= 32 in all)
         const uint32_t cols = n_tiles <= 1 ? 128u : n_tiles == 2 ? 256u : 512u;
@@ -202,7 +202,9 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
+        // the dense matrices into U; ends with a block-wide barrier behind a proxy fence (covers the small tables, the
+        // mbarriers and the TMEM address as well)
+        tc5_load_matrices<T>(tile, a.tc, a.d.partial != 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         tile.tmem = *tmem_slot + tl * 128;
     }

@@ -71,25 +71,48 @@ void push_kfrag(std::vector<uint8_t>& img, const HostField& f, const Fe& pow32_m
             }
 }
 
+// Layout 1, operands that are UNREDUCED products of two Montgomery residues (64 bytes, value = x y R^2 for the true x y):
+// the table of the constant c has 64 rows, row k = bytes of (c R^-1 256^k 2^32 mod p), so that the sweep's Montgomery row
+// leaves c x y R.  Several constants that multiply the SAME operand are stacked along N -- one tcgen05.mma then fills
+// 32 columns per constant: [16-byte K chunk 0..3][constant 0..n-1][column 0..31][16 bytes], 2 n KiB.
+void push_stack_wide(std::vector<uint8_t>& img, const HostField& f, const Fe pow_mont[64], const std::vector<Fe>& c_mont) {
+    std::vector<std::vector<Fe>> tab(c_mont.size(), std::vector<Fe>(64));
+    for (size_t b = 0; b < c_mont.size(); b++)
+        for (int k = 0; k < 64; k++) tab[b][k] = hf_from_mont(f, hf_from_mont(f, hf_mul(f, c_mont[b], pow_mont[k])));
+    for (int chunk = 0; chunk < 4; chunk++)
+        for (size_t b = 0; b < c_mont.size(); b++)
+            for (int col = 0; col < 32; col++)
+                for (int i = 0; i < 16; i++) img.push_back(byte_of(tab[b][16 * chunk + i], col));
+}
+
 }  // namespace
 
-bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why) {
+bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why, uint32_t layout) {
     auto no = [&](const char* m) {
         if (why) *why = m;
         return false;
     };
-    if (t < 2 || t > 5) return no("width outside [2,5]");
-    // column sums: at most 32 (t + 1) products of two bytes (the second row 0 of a pair of partial rounds has t + 1
-    // terms) plus one constant byte; pair-combining needs sum * 257 < 2^32
-    const uint64_t colmax = 32ull * (t + 1) * 255 * 255 + 255;
+    if (t < 2 || t > (layout == 1 ? 4u : 5u)) return no(layout == 1 ? "width outside [2,4]" : "width outside [2,5]");
+    // column sums, in units of 32 products of two bytes.  Layout 0: at most t + 1 values of 32 bytes (the second row 0 of
+    // a pair of partial rounds) plus one constant byte.  Layout 1: an S-box output is 64 bytes (two units); a full round
+    // sums t of them, the second row 0 two of them and t - 1 lanes; the constant is added after the pair-combine.
+    // Pair-combining needs sum * 257 < 2^32.
+    const uint64_t units = layout == 1 ? (2 * t > t + 3 ? 2 * t : t + 3) : t + 1;
+    const uint64_t colmax = 32ull * units * 255 * 255 + (layout == 1 ? 0 : 255);
     if (colmax * 257 >= (1ull << 32)) return no("column sums too large for the pair-combine");
-    // sweep input V < colmax * 256^32 * 256/255 ; result (V + m p) / 2^32 < V / 2^32 + p must stay below 2^256 and,
-    // for the lazy S-box (BN254), inside its operand range 2 a + p < 2^256 with the output below 2^256
+    // sweep input V < colmax * 256^32 * 256/255 (+ K' < p in layout 1); result (V + m p) / 2^32 < V / 2^32 + p must stay
+    // below 2^256 and, for the lazy S-box (BN254), inside its operand range 2 a + p < 2^256 with the output below 2^256
     long double p = 0;
     for (int k = 3; k >= 0; k--) p = p * 0x1p64L + (long double)f.p[k];
-    const long double vmax = (long double)colmax * 0x1p256L * (256.0L / 255.0L);
+    const long double vmax = (long double)colmax * 0x1p256L * (256.0L / 255.0L) + (layout == 1 ? p : 0.0L);
     const long double res = vmax / 0x1p32L + p;
     if (res >= 0x1p256L) return no("sweep results do not fit 256 bits");
+    if (layout == 1) {
+        // sqr_wide doubles its operand into eight limbs; the closing conditional subtraction needs a value below 2p
+        if (res >= 0x1p255L) return no("sweep results do not fit the squaring's operand range");
+        if (res >= 2 * p) return no("sweep results are not below 2p");
+        return true;
+    }
     if (f.bits == 254) {
         const long double q = p / 0x1p256L;
         long double y = res / p;
@@ -113,7 +136,7 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
     img.clear();
     const uint32_t half = full_rounds / 2, rp = partial_rounds, n = t - 1, total = full_rounds + rp;
     if (half == 0 || full_rounds - half == 0) return;
-    if (!tc_bounds_ok(f, t, nullptr)) return;
+    if (!tc_bounds_ok(f, t, nullptr, layout)) return;
 
     // the regrouped constants, from a scratch image
     PermDesc od{};
@@ -139,25 +162,67 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
     const Fe pow32 = pow2(32);
     auto here = [&img]() { return (uint32_t)img.size(); };
 
-    td.mat_off = here();
-    for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, mds[i], layout);
-    if (rp) {
-        td.pre_off = here();
-        for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, m_pre[i], layout);
-    }
-    td.ident_off = here();
-    push_frag(img, f, pow_mont, hf_one(f), layout);
-    td.part_off = here();
-    for (uint32_t i = 0; i < rp; i++) {
-        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j], layout);
-        for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j], layout);
-    }
-    // pairs of partial rounds (an odd count leaves the FIRST round on its own): c_q = sum_j w_j(i+1) v_j(i)
-    td.pair_off = here();
-    for (uint32_t i = rp & 1; i + 1 < rp; i += 2) {
-        Fe c = hf_zero();
-        for (uint32_t j = 0; j < n; j++) c = hf_add(f, c, hf_mul(f, w[i + 1][j], v[i][j]));
-        push_frag(img, f, pow_mont, c, layout);
+    if (layout == 1) {
+        // 64-row tables for the S-box outputs, stacked by the operand they multiply (see push_stack_wide)
+        Fe pow64[64];
+        for (int k = 0; k < 64; k++) pow64[k] = pow2(8 * k + 32);
+        auto column = [&](const std::vector<Fe>& m, uint32_t j) {
+            std::vector<Fe> c;
+            for (uint32_t i = 0; i < t; i++) c.push_back(m[i * t + j]);
+            return c;
+        };
+        td.mat_off = here();   // [T] stacks: column j of the dense matrix (what multiplies S-box output j, for every row)
+        for (uint32_t j = 0; j < t; j++) push_stack_wide(img, f, pow64, column(mds, j));
+        if (rp) {
+            td.pre_off = here();
+            for (uint32_t j = 0; j < t; j++) push_stack_wide(img, f, pow64, column(m_pre, j));
+        }
+        td.ident_off = here();
+        push_frag(img, f, pow_mont, hf_one(f), 1);
+        td.red_off = here();
+        push_stack_wide(img, f, pow64, {hf_one(f)});
+        td.m00_off = here();
+        push_stack_wide(img, f, pow64, {mds[0]});
+        // per partial round: w_1.. (32-row tables, they multiply lanes), then the stack (M00, v_1, ..) that multiplies the
+        // round's S-box output: row 0 and every lane in one operand
+        td.part_off = here();
+        for (uint32_t i = 0; i < rp; i++) {
+            for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j], 1);
+            std::vector<Fe> c{mds[0]};
+            for (uint32_t j = 0; j < n; j++) c.push_back(v[i][j]);
+            push_stack_wide(img, f, pow64, c);
+        }
+        // per pair (i, i+1): the stack (c_q, v_1(i), ..) that multiplies the FIRST round's S-box output in the pair's
+        // second step, c_q = sum_j w_j(i+1) v_j(i)
+        td.pair_off = here();
+        for (uint32_t i = rp & 1; i + 1 < rp; i += 2) {
+            Fe c = hf_zero();
+            for (uint32_t j = 0; j < n; j++) c = hf_add(f, c, hf_mul(f, w[i + 1][j], v[i][j]));
+            std::vector<Fe> cs{c};
+            for (uint32_t j = 0; j < n; j++) cs.push_back(v[i][j]);
+            push_stack_wide(img, f, pow64, cs);
+        }
+    } else {
+        td.mat_off = here();
+        for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, mds[i], layout);
+        if (rp) {
+            td.pre_off = here();
+            for (uint32_t i = 0; i < t * t; i++) push_frag(img, f, pow_mont, m_pre[i], layout);
+        }
+        td.ident_off = here();
+        push_frag(img, f, pow_mont, hf_one(f), layout);
+        td.part_off = here();
+        for (uint32_t i = 0; i < rp; i++) {
+            for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, w[i][j], layout);
+            for (uint32_t j = 0; j < n; j++) push_frag(img, f, pow_mont, v[i][j], layout);
+        }
+        // pairs of partial rounds (an odd count leaves the FIRST round on its own): c_q = sum_j w_j(i+1) v_j(i)
+        td.pair_off = here();
+        for (uint32_t i = rp & 1; i + 1 < rp; i += 2) {
+            Fe c = hf_zero();
+            for (uint32_t j = 0; j < n; j++) c = hf_add(f, c, hf_mul(f, w[i + 1][j], v[i][j]));
+            push_frag(img, f, pow_mont, c, layout);
+        }
     }
     // additive constants in execution order, t per round: what round r's outputs receive is what round r + 1
     // adds before its S-boxes
@@ -179,15 +244,59 @@ void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint3
     td.ok = 1;
 }
 
+namespace {
+// V (nine 32-bit limbs, V[0..8]) -> (V + m p) / 2^32, eight limbs
+void host_mont_row(const HostField& f, const uint32_t* v, uint32_t* out8) {
+    const uint32_t p32[8] = {(uint32_t)f.p[0], (uint32_t)(f.p[0] >> 32), (uint32_t)f.p[1], (uint32_t)(f.p[1] >> 32),
+                             (uint32_t)f.p[2], (uint32_t)(f.p[2] >> 32), (uint32_t)f.p[3], (uint32_t)(f.p[3] >> 32)};
+    const uint32_t m = v[0] * (uint32_t)f.np0;
+    uint64_t c = 0;
+    uint32_t r[10];
+    for (int l = 0; l < 9; l++) {
+        const unsigned __int128 ss = (unsigned __int128)v[l] + (l < 8 ? (unsigned __int128)m * p32[l] : 0) + c;
+        r[l] = (uint32_t)ss;
+        c = (uint64_t)(ss >> 32);
+    }
+    for (int l = 0; l < 8; l++) out8[l] = r[l + 1];
+}
+}  // namespace
+
+void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms, const uint8_t* kbytes, uint32_t* out8) {
+    uint64_t col[32] = {0};
+    for (uint32_t j = 0; j < n_terms; j++) {
+        const Tc5HostTerm& t = terms[j];
+        for (uint32_t k = 0; k < t.nbytes; k++) {
+            const uint32_t byte = (t.value[k / 4] >> (8 * (k % 4))) & 0xff;
+            for (int c = 0; c < 32; c++)
+                col[c] += (uint64_t)byte * t.table[(k / 16) * (t.stack * 512) + t.block * 512 + c * 16 + (k % 16)];
+        }
+    }
+    // the device pair-combines columns in 32 bits: the sums must leave room for that
+    for (int c = 0; c < 32; c++)
+        if (col[c] * 257 >= (1ull << 32)) {
+            for (int l = 0; l < 8; l++) out8[l] = 0xdeadbeefu;
+            return;
+        }
+    uint32_t v[10] = {0};
+    unsigned __int128 carry = 0;
+    for (int l = 0; l < 9; l++) {
+        unsigned __int128 s = carry;
+        for (int b = 0; b < 4; b++)
+            if (4 * l + b < 32) s += (unsigned __int128)col[4 * l + b] << (8 * b);
+        if (kbytes && l < 8)
+            s += (uint32_t)kbytes[4 * l] | ((uint32_t)kbytes[4 * l + 1] << 8) | ((uint32_t)kbytes[4 * l + 2] << 16) |
+                 ((uint32_t)kbytes[4 * l + 3] << 24);
+        v[l] = (uint32_t)s;
+        carry = s >> 32;
+    }
+    host_mont_row(f, v, out8);
+}
+
 void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const uint8_t* const* frags, const uint8_t* kfrag,
-                 uint32_t* out8, uint32_t layout) {
+                 uint32_t* out8) {
     // column sums, read back from the table layout
     uint64_t col[32];
     for (int c = 0; c < 32; c++) {
-        if (layout == 1) {
-            col[c] = kfrag[c];
-            continue;
-        }
         const int nt = c / 8, tg = (c % 8) / 2, e = c % 2;
         const uint8_t* q = kfrag + ((nt * 4 + tg) * 4 + e) * 4;
         col[c] = (uint64_t)q[0] | ((uint64_t)q[1] << 8) | ((uint64_t)q[2] << 16) | ((uint64_t)q[3] << 24);
@@ -198,8 +307,7 @@ void tc_host_row(const HostField& f, const uint32_t* x, uint32_t n_terms, const 
             for (int c = 0; c < 32; c++) {
                 const int nt = c / 8, g = c % 8;
                 const int tg = (k % 16) / 4, i = k % 4, hi = k / 16;
-                const uint8_t tb = layout == 1 ? frags[j][(k / 16) * 512 + c * 16 + (k % 16)]
-                                               : frags[j][((nt * 32 + (4 * g + tg)) * 2 + hi) * 4 + i];
+                const uint8_t tb = frags[j][((nt * 32 + (4 * g + tg)) * 2 + hi) * 4 + i];
                 col[c] += (uint64_t)byte * tb;
             }
         }

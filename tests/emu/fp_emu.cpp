@@ -303,7 +303,7 @@ extern "C" int emu_fp52_bounds(int field, uint32_t rate, uint32_t capacity, uint
 
 template <class F, int T, int ALPHA>
 static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf) {
-    const uint32_t kb = td.layout == 1 ? kTc5KBytes : kTcKBytes, lay = td.layout;
+    const uint32_t kb = kTcKBytes;
     for (int j = 0; j < T; j++) {
         uint32_t c[8];
         cload8(c, d.ark_off + j * 8);
@@ -320,7 +320,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
         for (int i = 0; i < T; i++) {
             const uint8_t* frags[T];
             for (int j = 0; j < T; j++) frags[j] = mat + (i * T + j) * kTcFragBytes;
-            tc_host_row(hf, &y[0][0], T, frags, kp + i * kb, st[i], lay);
+            tc_host_row(hf, &y[0][0], T, frags, kp + i * kb, st[i]);
         }
         kp += T * kb;
     };
@@ -341,13 +341,13 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                 frags[j] = part + (j - 1) * kTcFragBytes;
             }
             uint32_t n0[8];
-            tc_host_row(hf, &terms[0][0], T, frags, kp, n0, lay);
+            tc_host_row(hf, &terms[0][0], T, frags, kp, n0);
             for (int j = 1; j < T; j++) {
                 uint32_t two[2][8];
                 memcpy(two[0], st[0], 32);   // y
                 memcpy(two[1], st[j], 32);   // the lane
                 const uint8_t* fr[2] = {part + (T - 1 + j - 1) * kTcFragBytes, tab + td.ident_off};
-                tc_host_row(hf, &two[0][0], 2, fr, kp + j * kb, st[j], lay);
+                tc_host_row(hf, &two[0][0], 2, fr, kp + j * kb, st[j]);
             }
             memcpy(st[0], n0, 32);
             kp += round_k;
@@ -369,7 +369,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                     memcpy(terms[j], st[j], 32);
                     frags[j] = part + (j - 1) * kTcFragBytes;
                 }
-                tc_host_row(hf, &terms[0][0], T, frags, kp, x1, lay);
+                tc_host_row(hf, &terms[0][0], T, frags, kp, x1);
             }
             memcpy(y1, x1, 32);
             tc_sbox<F, ALPHA>(y1);
@@ -384,7 +384,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                     memcpy(terms[j + 1], st[j], 32);
                     frags[j + 1] = part + round_part + (j - 1) * kTcFragBytes;
                 }
-                tc_host_row(hf, &terms[0][0], T + 1, frags, kp + round_k, x2, lay);
+                tc_host_row(hf, &terms[0][0], T + 1, frags, kp + round_k, x2);
             }
             for (int j = 1; j < T; j++) {
                 uint32_t three[3][8];
@@ -393,7 +393,7 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
                 memcpy(three[2], st[j], 32);
                 const uint8_t* fr[3] = {part + round_part + (T - 1 + j - 1) * kTcFragBytes, part + (T - 1 + j - 1) * kTcFragBytes,
                                         tab + td.ident_off};
-                tc_host_row(hf, &three[0][0], 3, fr, kp + round_k + j * kb, st[j], lay);
+                tc_host_row(hf, &three[0][0], 3, fr, kp + round_k + j * kb, st[j]);
             }
             memcpy(st[0], x2, 32);
             kp += 2 * round_k;
@@ -406,6 +406,131 @@ static void emu_perm_tc_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDes
         uint32_t x[8];
         memcpy(x, st[j], 32);
         cond_sub_p<F>(st[j], x);
+    }
+}
+
+// ---- host model of VARIANT 7: 64-byte unreduced S-box values against the stacked 64-row tables of layout 1, every
+// reduction (the squarings' too) as a table contraction + sweep, exactly the sequence of poseidon_tc5.cuh.
+template <class F, int ALPHA>
+static void emu_tc5_pow(uint32_t* wide16, const uint32_t* x, const uint8_t* red, const HostField& hf) {
+    uint32_t y[8], w[16];
+    memcpy(y, x, 32);
+    for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) {
+        sqr_wide(w, y);
+        const Tc5HostTerm term{w, 64, red, 1, 0};
+        tc5_host_row(hf, &term, 1, nullptr, y);
+    }
+    mul_wide(wide16, y, x);
+}
+
+template <class F, int T, int ALPHA>
+static void emu_perm_tc5_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf) {
+    constexpr uint32_t N = T - 1, kStack = 2 * T * 1024, kRoundPart = N * 1024 + kStack, kb = kTc5KBytes;
+    for (int j = 0; j < T; j++) {
+        uint32_t c[8];
+        cload8(c, d.ark_off + j * 8);
+        fp_add<F>(st[j], st[j], c);
+    }
+    const uint32_t half = d.half_full, rp = d.partial;
+    const uint8_t* kp = tab + td.k_off;
+    const uint8_t* red = tab + td.red_off;
+    const uint8_t* m00 = tab + td.m00_off;
+    const uint8_t* ident = tab + td.ident_off;
+    auto full_round = [&](const uint8_t* mat) {
+        uint32_t y[T][16];
+        for (int j = 0; j < T; j++) emu_tc5_pow<F, ALPHA>(y[j], st[j], red, hf);
+        for (int i = 0; i < T; i++) {
+            Tc5HostTerm terms[T];
+            for (int j = 0; j < T; j++) terms[j] = Tc5HostTerm{y[j], 64, mat + j * kStack, (uint32_t)T, (uint32_t)i};
+            tc5_host_row(hf, terms, T, kp + i * kb, st[i]);
+        }
+        kp += T * kb;
+    };
+    for (uint32_t r = 0; r < half; r++) full_round(tab + ((r + 1 == half && rp) ? td.pre_off : td.mat_off));
+    if (rp) {
+        const uint8_t* part = tab + td.part_off;   // per round: w [N KiB], stack (M00, v) [2 T KiB]
+        const uint8_t* pair = tab + td.pair_off;   // per pair: stack (c_q, v(i))
+        if (rp & 1) {
+            uint32_t y0[16], n0[8];
+            emu_tc5_pow<F, ALPHA>(y0, st[0], red, hf);
+            const uint8_t* stack = part + N * 1024;
+            {
+                Tc5HostTerm terms[T];
+                terms[0] = Tc5HostTerm{y0, 64, stack, (uint32_t)T, 0};
+                for (int j = 1; j < T; j++) terms[j] = Tc5HostTerm{st[j], 32, part + (j - 1) * 1024, 1, 0};
+                tc5_host_row(hf, terms, T, kp, n0);
+            }
+            for (int j = 1; j < T; j++) {
+                uint32_t lane[8];
+                memcpy(lane, st[j], 32);
+                const Tc5HostTerm terms[2] = {Tc5HostTerm{y0, 64, stack, (uint32_t)T, (uint32_t)j}, Tc5HostTerm{lane, 32, ident, 1, 0}};
+                tc5_host_row(hf, terms, 2, kp + j * kb, st[j]);
+            }
+            memcpy(st[0], n0, 32);
+            kp += T * kb;
+            part += kRoundPart;
+        }
+        for (uint32_t q = 0; q < rp / 2; q++) {
+            const bool last = q + 1 == rp / 2;
+            uint32_t y0[16], y1[16], x1[8], x2[8];
+            emu_tc5_pow<F, ALPHA>(y0, st[0], red, hf);
+            {
+                Tc5HostTerm terms[T];
+                terms[0] = Tc5HostTerm{y0, 64, m00, 1, 0};
+                for (int j = 1; j < T; j++) terms[j] = Tc5HostTerm{st[j], 32, part + (j - 1) * 1024, 1, 0};
+                tc5_host_row(hf, terms, T, kp, x1);
+            }
+            emu_tc5_pow<F, ALPHA>(y1, x1, red, hf);
+            const uint8_t* wb = part + kRoundPart;
+            const uint8_t* by1 = wb + N * 1024;
+            {
+                Tc5HostTerm terms[T + 1];
+                terms[0] = Tc5HostTerm{y1, 64, by1, (uint32_t)T, 0};
+                terms[1] = Tc5HostTerm{y0, 64, pair, (uint32_t)T, 0};
+                for (int j = 1; j < T; j++) terms[j + 1] = Tc5HostTerm{st[j], 32, wb + (j - 1) * 1024, 1, 0};
+                tc5_host_row(hf, terms, T + 1, kp + T * kb, x2);
+            }
+            for (int j = 1; j < T; j++) {
+                uint32_t lane[8];
+                memcpy(lane, st[j], 32);
+                const Tc5HostTerm terms[3] = {Tc5HostTerm{y1, 64, by1, (uint32_t)T, (uint32_t)j},
+                                              Tc5HostTerm{y0, 64, pair, (uint32_t)T, (uint32_t)j}, Tc5HostTerm{lane, 32, ident, 1, 0}};
+                // the device adds the lanes' constant only behind the last partial round; before that it is zero
+                tc5_host_row(hf, terms, 3, last ? kp + T * kb + j * kb : nullptr, st[j]);
+            }
+            memcpy(st[0], x2, 32);
+            kp += 2 * T * kb;
+            part += 2 * kRoundPart;
+            pair += kStack;
+        }
+    }
+    for (uint32_t r = half + rp; r < d.total; r++) full_round(tab + td.mat_off);
+    for (int j = 0; j < T; j++) {
+        uint32_t x[8];
+        memcpy(x, st[j], 32);
+        cond_sub_p<F>(st[j], x);
+    }
+}
+
+template <class F, int T>
+static int emu_perm_tc5_a(uint64_t alpha, const PermDesc& d, const TcDesc& td, const uint8_t* tab, const HostField& hf, uint32_t* states,
+                          size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        uint32_t s[T][8];
+        memcpy(s, states + i * T * 8, sizeof s);
+        if (alpha == 5) emu_perm_tc5_one<F, T, 5>(s, d, td, tab, hf);
+        else if (alpha == 17) emu_perm_tc5_one<F, T, 17>(s, d, td, tab, hf);
+        else return 1;
+        memcpy(states + i * T * 8, s, sizeof s);
+    }
+    return 0;
+}
+
+// the unreduced products on their own: out (16 words) = a * b, or a^2 when b is null
+extern "C" void emu_mul_wide(const uint32_t* a, const uint32_t* b, uint32_t* out, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        if (b) mul_wide(out + 16 * i, a + 8 * i, b + 8 * i);
+        else sqr_wide(out + 16 * i, a + 8 * i);
     }
 }
 
@@ -449,6 +574,22 @@ extern "C" int emu_permute_tc_layout(int field, uint32_t rate, uint32_t capacity
             c_pool[j * 8 + 2 * k + 1] = (uint32_t)(ark[j].v[k] >> 32);
         }
     d.half_full = rf / 2; d.partial = rp; d.total = rounds; d.rate = rate; d.capacity = capacity;
+    if (layout == 1) {
+        if (field == 0) {
+            switch (t) {
+                case 2: return emu_perm_tc5_a<Bn254Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
+                case 3: return emu_perm_tc5_a<Bn254Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
+                case 4: return emu_perm_tc5_a<Bn254Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+            }
+        } else {
+            switch (t) {
+                case 2: return emu_perm_tc5_a<Bls12381Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
+                case 3: return emu_perm_tc5_a<Bls12381Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
+                case 4: return emu_perm_tc5_a<Bls12381Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+            }
+        }
+        return -1;
+    }
     if (field == 0) {
         switch (t) {
             case 2: return emu_perm_tc_a<Bn254Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);

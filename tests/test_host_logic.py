@@ -398,8 +398,33 @@ def test_tensor_core_variant_host_model(emu, ref, name):
         rc = emu.emu_permute_tc_layout(fid, cfg.rate, cfg.capacity, cfg.full_rounds, cfg.partial_rounds, C.c_uint64(cfg.alpha),
                                        C.c_void_p(ark.ctypes.data), C.c_void_p(mds.ctypes.data), C.c_void_p(s.ctypes.data),
                                        C.c_size_t(n), layout)
-        if cfg.alpha not in (5, 17):
+        if cfg.alpha not in (5, 17) or (layout == 1 and t > 4):   # variant 7: four values per 128-column tile
             assert rc == 1
             continue
         assert rc == 0
         assert np.array_equal(s.view(np.uint64), exp), layout
+
+
+def test_unreduced_products(emu):
+    """mul_wide / sqr_wide (fp256.cuh, the S-box of variant 7): exact 512-bit products, worst-case limbs included."""
+    rng = np.random.default_rng(11)
+    n = 64
+    a = rng.integers(0, 2**32, size=(n, 8), dtype=np.uint64).astype(np.uint32)
+    b = rng.integers(0, 2**32, size=(n, 8), dtype=np.uint64).astype(np.uint32)
+    a[0] = 0xffffffff
+    b[0] = 0xffffffff
+    a[1] = 0
+    a[2] = 0xffffffff
+    a[2, 7] = 0x7fffffff
+    a[3] = 0x80000000
+    a[3, 7] = 0x40000000
+
+    def ints(x):
+        return [sum(int(w) << (32 * k) for k, w in enumerate(row)) for row in x]
+    out = np.zeros((n, 16), dtype=np.uint32)
+    emu.emu_mul_wide(C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(out.ctypes.data), C.c_size_t(n))
+    assert ints(out) == [x * y for x, y in zip(ints(a), ints(b))]
+    sq_in = a.copy()
+    sq_in[:, 7] &= 0x7fffffff   # the squaring's operand range: below 2^255
+    emu.emu_mul_wide(C.c_void_p(sq_in.ctypes.data), None, C.c_void_p(out.ctypes.data), C.c_size_t(n))
+    assert ints(out) == [x * x for x in ints(sq_in)]
