@@ -358,7 +358,11 @@ LaunchCfg sponge_cfg(const psd_ctx* ctx, const SpongeKernelEntry* k, uint64_t n)
         const uint64_t max_block = (uint64_t)k->max_block;
         const uint64_t per_sm = (n + sms - 1) / sms;
         cfg.block = (int)std::min<uint64_t>(max_block, std::max<uint64_t>(32, (per_sm + 31) / 32 * 32));
-        if (k->variant == 7) cfg.block = (cfg.block + 127) / 128 * 128;   // whole 128-sponge tiles
+        if (k->variant == 7) {
+            cfg.block = (cfg.block + 127) / 128 * 128;   // whole 128-sponge tiles
+            static const int tiles_cap = env_int("PSD_TC5_TILES", 0);   // tuning runs
+            if (tiles_cap > 0) cfg.block = std::min(cfg.block, tiles_cap * 128);
+        }
     } else if (k->variant == 5) {
         // Variant 5's partial-round body (1.5 K instructions) does not fit the instruction caches when
         // the warps of a scheduler sit at different places in it.  Warps of ONE block start together and

@@ -53,6 +53,12 @@ PSD_HD constexpr uint32_t tc5_stage_bytes(uint32_t t) { return (6 * t - 2) * 102
 PSD_HD constexpr uint32_t tc5_u_bytes(uint32_t t, uint32_t tiles) {
     return 4 * t * t * 1024 > tiles * tc5_stage_bytes(t) ? 4 * t * t * 1024 : tiles * tc5_stage_bytes(t);
 }
+// TMEM columns a block of `tiles` tiles allocates: 32 t per tile, rounded up to a power of two >= 32
+PSD_HD constexpr uint32_t tc5_tmem_cols(uint32_t t, uint32_t tiles) {
+    uint32_t c = 32;
+    while (c < 32 * t * tiles) c *= 2;
+    return c;
+}
 PSD_HD constexpr uint32_t tc5_smem_bytes(uint32_t t, uint32_t tiles) {
     return tc5_small_bytes() + tiles * tc5_a_bytes(t) + tc5_u_bytes(t, tiles) + 128;
 }
@@ -65,7 +71,6 @@ struct Tc5Tile {
     uint32_t stage_u32;       // ... of the tile's staging buffer (inside U)
     uint32_t small_u32;       // ... of the block's small tables
     uint32_t u_u32;           // ... of U
-    uint32_t u_bytes;         // matrices to restore into U after the partial rounds
     // Two mbarriers per tile: a step commits twice (row 0 first, the lanes behind it), and a waiter may be at most one
     // phase behind an mbarrier, so the two completions must not share one.
     uint32_t mbar_u32[2];
@@ -74,7 +79,7 @@ struct Tc5Tile {
     const unsigned char* tab; // the context's table image in global memory (layout 1)
     int row;                  // this thread's row in the tile, 0..127
     int bar_id;               // named barrier of the tile
-    bool leader;              // the thread that issues the tile's MMAs
+    bool leader_warp;         // warp-uniform: the tile's first warp, one elected thread of which issues the tile's MMAs
 };
 
 __device__ __forceinline__ uint64_t tc5_desc(uint32_t saddr, uint32_t lbo) {
@@ -98,6 +103,15 @@ __device__ __forceinline__ void tc5_mma_wide(uint32_t d, uint32_t a_u32, uint32_
 }
 __device__ __forceinline__ void tc5_commit(const Tc5Tile& t, int which) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(t.mbar_u32[which]) : "memory");
+}
+
+// One thread of a converged warp.  The MMAs are issued from warp-uniform control flow with warp-uniform operands (the tile
+// index comes through a shuffle, see sponge_kernel.cuh): behind a per-thread predicate ptxas wraps every instruction in a
+// broadcast loop that ALL warps execute (measured: 11 % of the kernel's instructions).
+__device__ __forceinline__ bool tc5_elect() {
+    uint32_t pred = 0;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 
 // this thread's bytes of a value -> A slot at byte offset `off` of the tile's A region
@@ -222,21 +236,6 @@ __device__ __forceinline__ void tc5_load_matrices(const Tc5Tile& t, const TcDesc
     __syncthreads();
 }
 
-// y (8 limbs, < 2^255) <- (w mod p) R^-1-adjusted, w = the 64-byte value just stored at slot `off`: one trip through the
-// tensor core against the reduction table, result in tile column block 0
-template <class F>
-__device__ __forceinline__ void tc5_reduce(uint32_t* y, uint32_t off, uint32_t d_col, Tc5Tile& t) {
-    tc5_step_begin(t);
-    if (t.leader) {
-        tc5_mma_wide(t.tmem + d_col, t.a_u32 + off, t.small_u32 + 3 * 1024, 1, false);
-        tc5_commit(t, 0);
-    }
-    tc5_wait(t, 0);
-    int c[32];
-    tc5_load(t, d_col, c);
-    tc5_sweep<F, false>(y, c, nullptr);
-}
-
 // x^(ALPHA - 1) of a sweep result, by the integer pipe alone (PSD_TC5_SQTC == 0): the lazy squarings of tc_sbox
 template <class F, int ALPHA>
 __device__ __forceinline__ void tc5_pow_int(uint32_t* y, uint32_t* in, const uint32_t* x) {
@@ -252,10 +251,26 @@ __device__ __forceinline__ void tc5_pow_int(uint32_t* y, uint32_t* in, const uin
     for (int q = 1; q < (ALPHA == 5 ? 2 : 4); q++) fp_sqr<F, !kLazy>(y, y);
 }
 
-// the S-box of ONE value: x -> the unreduced 64 bytes of x^ALPHA in the wide slot at `off`
-template <class F, int ALPHA>
-__device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, Tc5Tile& t) {
+// the S-box of ONE value: x -> the unreduced 64 bytes of x^ALPHA in the wide slot at `off`.
+// SHADOW: the lane columns of the previous step (tile columns 32 j, complete) are swept and written back to their A slots
+// while the first reduction is on its way through the tensor core -- work that depends on nothing in the S-box chain.
+template <class F, int T, int ALPHA, bool SHADOW>
+__device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, Tc5Tile& t, bool lanes_pending = false,
+                                              uint32_t lane_off = 0) {
     uint32_t y[8], in[8], w[16];
+    auto lanes = [&]() {
+        if (SHADOW && lanes_pending) {
+            __syncwarp();   // behind the one-thread issue block; the TMEM loads are warp-collective
+#pragma unroll
+            for (int j = 1; j < T; j++) {
+                int c[32];
+                uint32_t lane[8];
+                tc5_load(t, 32 * j, c);
+                tc5_sweep<F, false>(lane, c, nullptr);
+                tc5_store_a(t, lane_off + (j - 1) * kTc5Narrow, lane);
+            }
+        }
+    };
 #if PSD_TC5_SQTC
 #pragma unroll
     for (int k = 0; k < 8; k++) in[k] = y[k] = x[k];
@@ -263,9 +278,19 @@ __device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, T
     for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) {
         sqr_wide(w, y);
         tc5_store_wide(t, off, w);
-        tc5_reduce<F>(y, off, 0, t);
+        tc5_step_begin(t);
+        if (t.leader_warp && tc5_elect()) {
+            tc5_mma_wide(t.tmem, t.a_u32 + off, t.small_u32 + 3 * 1024, 1, false);
+            tc5_commit(t, 0);
+        }
+        if (q == 0) lanes();
+        tc5_wait(t, 0);
+        int c[32];
+        tc5_load(t, 0, c);
+        tc5_sweep<F, false>(y, c, nullptr);
     }
 #else
+    lanes();
     tc5_pow_int<F, ALPHA>(y, in, x);
 #endif
     mul_wide(w, y, in);
@@ -291,7 +316,7 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
             tc5_store_wide(t, j * kTc5Wide, w);
         }
         tc5_step_begin(t);
-        if (t.leader) {
+        if (t.leader_warp && tc5_elect()) {
 #pragma unroll
             for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem + 32 * j, t.a_u32 + j * kTc5Wide, t.small_u32 + 3 * 1024, 1, false);
             tc5_commit(t, 0);
@@ -320,7 +345,7 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
         tc5_store_wide(t, j * kTc5Wide, w);
     }
     tc5_step_begin(t);
-    if (t.leader) {
+    if (t.leader_warp && tc5_elect()) {
 #pragma unroll
         for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem, t.a_u32 + j * kTc5Wide, mat_u32 + j * 2 * T * 1024, T, j > 0);
         tc5_commit(t, 0);
@@ -376,12 +401,13 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
         tc5_stage_commit();
 #pragma unroll
         for (int j = 1; j < T; j++) tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
+        bool lanes_pending = false;   // the last step's lane columns wait in TMEM for the next S-box's shadow
         if (rp & 1) {
             // an odd number of partial rounds: the first one on its own.  y0 against the stack (M00, v): row 0 and lanes
-            tc5_sbox_slot<F, ALPHA>(st[0], kY0, t);
+            tc5_sbox_slot<F, T, ALPHA, false>(st[0], kY0, t);
             tc5_stage_wait();
             tc5_step_begin(t);
-            if (t.leader) {
+            if (t.leader_warp && tc5_elect()) {
                 tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy1, T, false);
 #pragma unroll
                 for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWb + (j - 1) * kTc5Tab, 1, true);
@@ -397,30 +423,31 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
                 tc5_sweep<F, true>(st[0], c, kp);
             }
             tc5_wait(t, 1);
+            if (pairs) {
+                tc5_stage(t, sWa, part + kRoundPart, N * kTc5Tab);
+                tc5_stage(t, sBy0, pair, kStack);
+                tc5_stage(t, sWb, part + 2 * kRoundPart, kRoundPart);
+                tc5_stage_commit();
+                lanes_pending = true;
+            } else {
 #pragma unroll
-            for (int j = 1; j < T; j++) {
-                int c[32];
-                tc5_load(t, 32 * j, c);
-                tc5_sweep<F, true>(st[j], c, kp + j * kTc5KBytes);
-                if (pairs) tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
+                for (int j = 1; j < T; j++) {
+                    int c[32];
+                    tc5_load(t, 32 * j, c);
+                    tc5_sweep<F, true>(st[j], c, kp + j * kTc5KBytes);
+                }
             }
             kp += kRoundK;
             part += kRoundPart;
-            if (pairs) {
-                tc5_stage(t, sWa, part, N * kTc5Tab);
-                tc5_stage(t, sBy0, pair, kStack);
-                tc5_stage(t, sWb, part + kRoundPart, kRoundPart);
-                tc5_stage_commit();
-            }
         }
 #pragma unroll 1
         for (uint32_t q = 0; q < pairs; q++) {
             const bool last = q + 1 == pairs;
             // first round of the pair:  row 0 = M00 y0 + sum_j w_j(i) s_j
-            tc5_sbox_slot<F, ALPHA>(st[0], kY0, t);
+            tc5_sbox_slot<F, T, ALPHA, true>(st[0], kY0, t, lanes_pending, kLane);
             tc5_stage_wait();
             tc5_step_begin(t);
-            if (t.leader) {
+            if (t.leader_warp && tc5_elect()) {
                 tc5_mma_wide(t.tmem, t.a_u32 + kY0, m00_u32, 1, false);
 #pragma unroll
                 for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWa + (j - 1) * kTc5Tab, 1, true);
@@ -434,9 +461,9 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
             }
             // second round:  y1 (M00, v(i+1)) + y0 (c_q, v(i)) fill row 0 and the lanes' columns at once; the lanes add
             // w_j(i+1) s_j to row 0 and 1 s_j to their own columns
-            tc5_sbox_slot<F, ALPHA>(st[0], kY1, t);
+            tc5_sbox_slot<F, T, ALPHA, false>(st[0], kY1, t);
             tc5_step_begin(t);
-            if (t.leader) {
+            if (t.leader_warp && tc5_elect()) {
                 tc5_mma_wide(t.tmem, t.a_u32 + kY1, sBy1, T, false);
                 tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy0, T, true);
 #pragma unroll
@@ -452,6 +479,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
                 tc5_load(t, 0, c);
                 tc5_sweep<F, true>(st[0], c, kp + kRoundK);
             }
+            // every instruction that read the A slots and the staging buffers has completed
             tc5_wait(t, 1);
             if (last) {
                 // the last partial round's lanes receive the constants moved behind the partial rounds
@@ -462,18 +490,12 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
                     tc5_sweep<F, true>(st[j], c, kp + kRoundK + j * kTc5KBytes);
                 }
             } else {
-#pragma unroll
-                for (int j = 1; j < T; j++) {
-                    int c[32];
-                    tc5_load(t, 32 * j, c);
-                    tc5_sweep<F, false>(st[j], c, nullptr);
-                    tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
-                }
-                // every instruction that read the staging buffers has completed: the next pair's tables
+                // the next pair's tables; its first S-box sweeps this pair's lanes in its shadow
                 tc5_stage(t, sWa, part + 2 * kRoundPart, N * kTc5Tab);
                 tc5_stage(t, sBy0, pair + kStack, kStack);
                 tc5_stage(t, sWb, part + 3 * kRoundPart, kRoundPart);
                 tc5_stage_commit();
+                lanes_pending = true;
             }
             kp += 2 * kRoundK;
             part += 2 * kRoundPart;

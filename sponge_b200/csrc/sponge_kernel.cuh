@@ -92,12 +92,18 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #ifndef PSD_TC_BLOCK
 #define PSD_TC_BLOCK 512
 #endif
-#define PSD_SMEM_BLOCK(VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 5 || (VARIANT) == 7 ? 512 : 448)
+// Variant 7: whole 128-sponge tiles; a tile owns 32 T of the SM's 512 TMEM columns, so five tiles (96 registers per thread)
+// up to T = 3 and four (128 registers) at T = 4.
+#ifndef PSD_TC5_BLOCK
+#define PSD_TC5_BLOCK(T) ((T) <= 3 ? 640 : 512)
+#endif
+#define PSD_SMEM_BLOCK(T, VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 7 ? PSD_TC5_BLOCK(T) : (VARIANT) == 5 ? 512 : 448)
 #define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) >= 5 ? 1 : 2)
 #if defined(PSD_POOL_SHARED) && PSD_POOL_SHARED
 #define PSD_POOL_KIND 1
-#define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_SMEM_BLOCK(VARIANT), PSD_SMEM_BLOCKS(VARIANT))
-#define PSD_MAX_BLOCK(VARIANT) PSD_SMEM_BLOCK(VARIANT)
+#define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_SMEM_BLOCK(T, VARIANT), PSD_SMEM_BLOCKS(VARIANT))
+#define PSD_MAX_BLOCK(VARIANT) PSD_SMEM_BLOCK(3, VARIANT)
+#define PSD_MAX_BLOCK_T(T, VARIANT) PSD_SMEM_BLOCK(T, VARIANT)
 #else
 #define PSD_POOL_KIND 0
 #define PSD_LAUNCH_BOUNDS(T, VARIANT) __launch_bounds__(PSD_KERNEL_MAX_BLOCK(VARIANT), PSD_KERNEL_BLOCKS_AT_MAX(T, VARIANT))
@@ -165,13 +171,15 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
     Tc5Tile tile;
     if (VARIANT == 7) {
         unsigned char* base = reinterpret_cast<unsigned char*>(c_pool) + ((a.pool_words * 4u + 1023u) & ~1023u);
-        const uint32_t n_tiles = blockDim.x >> 7, tl = threadIdx.x >> 7;
+        // the tile index through a shuffle: warp-uniform to the compiler, so that everything derived from it (operand
+        // addresses, descriptors, the issuing branch) stays on the uniform datapath
+        const uint32_t n_tiles = blockDim.x >> 7, tl = __shfl_sync(0xffffffffu, threadIdx.x >> 7, 0);
         unsigned char* a0 = base + tc5_small_bytes();
         unsigned char* u0 = a0 + n_tiles * tc5_a_bytes(T);
         unsigned char* bars = u0 + tc5_u_bytes(T, n_tiles);
-        uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 64);
+        uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 120);
         tile.row = threadIdx.x & 127;
-        tile.leader = tile.row == 0;
+        tile.leader_warp = __shfl_sync(0xffffffffu, (threadIdx.x >> 5) & 3, 0) == 0;
         tile.bar_id = 1 + (int)tl;
         tile.tab = a.tc_tab;
         tile.a_ptr = a0 + tl * tc5_a_bytes(T);
@@ -182,7 +190,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         tile.mbar_u32[0] = (uint32_t)__cvta_generic_to_shared(bars + tl * 16);
         tile.mbar_u32[1] = tile.mbar_u32[0] + 8;
         tile.parity[0] = tile.parity[1] = 0;
-        if (tile.leader) {
+        if (tile.row == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tile.mbar_u32[0]));
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tile.mbar_u32[1]));
             asm volatile("fence.mbarrier_init.release.cluster;");
@@ -195,8 +203,8 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
             for (uint32_t q = threadIdx.x; q < 64; q += blockDim.x) sdst[128 + q] = __ldg(g + a.tc.ident_off / 16 + q);
             for (uint32_t q = threadIdx.x; q < 128; q += blockDim.x) sdst[192 + q] = __ldg(g + a.tc.red_off / 16 + q);
         }
-        // tensor memory: 128 columns per tile (a power of two >= 32 in all)
-        const uint32_t cols = n_tiles <= 1 ? 128u : n_tiles == 2 ? 256u : 512u;
+        // tensor memory: 32 T columns per tile (a power of two >= 32 in all)
+        const uint32_t cols = tc5_tmem_cols(T, n_tiles);
         if (threadIdx.x < 32) {
             asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"(cols));
             asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -206,7 +214,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         // mbarriers and the TMEM address as well)
         tc5_load_matrices<T>(tile, a.tc, a.d.partial != 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        tile.tmem = *tmem_slot + tl * 128;
+        tile.tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0) + tl * 32 * T;
     }
 #endif
     {
@@ -383,9 +391,8 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (threadIdx.x < 32) {
-            const uint32_t n_tiles = blockDim.x >> 7;
-            const uint32_t cols = n_tiles <= 1 ? 128u : n_tiles == 2 ? 256u : 512u;
-            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tile.tmem - (threadIdx.x >> 7) * 128), "r"(cols));
+            const uint32_t cols = tc5_tmem_cols(T, blockDim.x >> 7);
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tile.tmem), "r"(cols));   // warp 0: tile 0
         }
     }
 #endif

@@ -20,7 +20,7 @@ typedef Bls12381Fr TuField;
 
 #define PSD_REG_TC5(T, ALPHA)                                                                 \
     static SpongeKernelRegistrar g_reg_tc5_##T##_##ALPHA(SpongeKernelEntry{                   \
-        TuField::kFieldId, T, ALPHA, 7, 1, 0, PSD_MAX_BLOCK(7), sponge_kernel<TuField, T, ALPHA, 7>, \
+        TuField::kFieldId, T, ALPHA, 7, 1, 0, PSD_MAX_BLOCK_T(T, 7), sponge_kernel<TuField, T, ALPHA, 7>, \
         "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=7,smem>"});
 
 PSD_REG_TC5(3, 5)
