@@ -404,7 +404,8 @@ Resolved resolve_kernel(const psd_ctx* ctx, int ragged = 0) {
             return r;
         }
     }
-    if (ctx->variant >= 6 && !ragged && ctx->pl_tc && ctx->pl_tctab && ctx->tcd.ok) {
+    if ((ctx->variant == 6 || (ctx->variant > 6 && ctx->field == PSD_FIELD_BN254_FR)) && !ragged && ctx->pl_tc && ctx->pl_tctab &&
+        ctx->tcd.ok) {
         const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 6, kPoolSmem, nullptr, 0);
         if (k && k->variant == 6) {
             r.k = k, r.pl = ctx->pl_tc, r.d = &ctx->tdesc;
@@ -772,10 +773,11 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->capacity = p->capacity;
     ctx->t = t;
     ctx->alpha = p->alpha;
-    // Default request: the tensor-core form for BN254 (c2: 197 M perm/s against 174 M for variant 5); for BLS12-381
-    // (alpha = 17 S-boxes with full reductions dominate) it measured SLOWER than the all-integer variant 3 on c5
-    // (126 M against 169 M perm/s), so that field asks for 5 and gets 3; psd_ctx_set_variant(ctx, 6) still selects it.
-    ctx->variant = p->field == PSD_FIELD_BN254_FR ? 7 : 5;
+    // Default request: variant 7 (tcgen05 linear layer AND reductions; c2: 362 M perm/s against 220 M for variant 6,
+    // c5: 349 M against 169 M for variant 3).  Where variant 7 has no kernel the request degrades: BN254 to 6, then 5;
+    // BLS12-381 skips 6 (mma.sync form, S-box with full reductions: 126 M perm/s on c5, slower than the all-integer
+    // variant 3) unless psd_ctx_set_variant(ctx, 6) asks for exactly that.
+    ctx->variant = 7;
 
     // constants -> Montgomery
     const Fe* ark = reinterpret_cast<const Fe*>(p->ark);

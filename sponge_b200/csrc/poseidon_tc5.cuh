@@ -50,8 +50,11 @@ PSD_HD constexpr uint32_t tc5_a_bytes(uint32_t t) {
 // staging of a tile for one pair of partial rounds: w(i) [t-1], the stack (c_q, v(i)) [2t], w(i+1) [t-1], the stack
 // (M00, v(i+1)) [2t] KiB
 PSD_HD constexpr uint32_t tc5_stage_bytes(uint32_t t) { return (6 * t - 2) * 1024; }
+// U: both dense matrices (M and M_pre, 2 t^2 KiB each) up to t = 4, one at a time at t = 5 -- or the tiles' staging buffers
+PSD_HD constexpr bool tc5_both_matrices(uint32_t t) { return t <= 4; }
 PSD_HD constexpr uint32_t tc5_u_bytes(uint32_t t, uint32_t tiles) {
-    return 4 * t * t * 1024 > tiles * tc5_stage_bytes(t) ? 4 * t * t * 1024 : tiles * tc5_stage_bytes(t);
+    return (tc5_both_matrices(t) ? 4 : 2) * t * t * 1024 > tiles * tc5_stage_bytes(t) ? (tc5_both_matrices(t) ? 4 : 2) * t * t * 1024
+                                                                                       : tiles * tc5_stage_bytes(t);
 }
 // TMEM columns a block of `tiles` tiles allocates: 32 t per tile, rounded up to a power of two >= 32
 PSD_HD constexpr uint32_t tc5_tmem_cols(uint32_t t, uint32_t tiles) {
@@ -163,19 +166,32 @@ __device__ __forceinline__ void tc5_load(const Tc5Tile& t, uint32_t d_col, int (
 // 32 column sums (+ the additive constant K 2^32 mod p, eight limbs at kptr, if HASK) -> 8 limbs, value < p + 2^249:
 // columns 4l, 4l+1 and 4l+2, 4l+3 pair up (sum < 2^32 / 257), the pairs form two 256-bit numbers X + (Y << 16), then one
 // 32-bit Montgomery row -- the same sweep as variant 6, minus its exchange through shared memory
-template <class F, bool HASK>
+// BIG: column sums up to 2^31 (the full rounds at t = 5 add ten 32-product units): the four columns of a limb are combined
+// in 64 bits instead.
+template <class F, bool HASK, bool BIG = false>
 __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], const unsigned char* kptr) {
-    uint32_t X[8], Y[8];
+    uint32_t X[8], ys[9];
+    if (BIG) {
+        ys[0] = 0;
 #pragma unroll
-    for (int l = 0; l < 8; l++) {
-        X[l] = (uint32_t)c[4 * l] + ((uint32_t)c[4 * l + 1] << 8);
-        Y[l] = (uint32_t)c[4 * l + 2] + ((uint32_t)c[4 * l + 3] << 8);
+        for (int l = 0; l < 8; l++) {
+            const uint64_t w = (uint64_t)(uint32_t)c[4 * l] + ((uint64_t)(uint32_t)c[4 * l + 1] << 8) +
+                               ((uint64_t)(uint32_t)c[4 * l + 2] << 16) + ((uint64_t)(uint32_t)c[4 * l + 3] << 24);
+            X[l] = (uint32_t)w;
+            ys[l + 1] = (uint32_t)(w >> 32);
+        }
+    } else {
+        uint32_t Y[8];
+#pragma unroll
+        for (int l = 0; l < 8; l++) {
+            X[l] = (uint32_t)c[4 * l] + ((uint32_t)c[4 * l + 1] << 8);
+            Y[l] = (uint32_t)c[4 * l + 2] + ((uint32_t)c[4 * l + 3] << 8);
+        }
+        ys[0] = Y[0] << 16;
+#pragma unroll
+        for (int k = 1; k < 8; k++) ys[k] = __funnelshift_l(Y[k - 1], Y[k], 16);
+        ys[8] = Y[7] >> 16;
     }
-    uint32_t ys[9];
-    ys[0] = Y[0] << 16;
-#pragma unroll
-    for (int k = 1; k < 8; k++) ys[k] = __funnelshift_l(Y[k - 1], Y[k], 16);
-    ys[8] = Y[7] >> 16;
     uint32_t v[9];
     asm("add.cc.u32 %0, %9, %18;\n\t"
         "addc.cc.u32 %1, %10, %19;\n\t"
@@ -222,13 +238,14 @@ __device__ __forceinline__ void tc5_stage_commit() { asm volatile("cp.async.comm
 __device__ __forceinline__ void tc5_stage_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // The dense matrices' stacks, image -> U, by the whole block; ends with everything visible to the tensor core.
+// first_off: the matrix that goes to the front of U; second_off: the one behind it, or 0 for none.
 template <int T>
-__device__ __forceinline__ void tc5_load_matrices(const Tc5Tile& t, const TcDesc& td, bool with_pre) {
+__device__ __forceinline__ void tc5_load_matrices(const Tc5Tile& t, uint32_t first_off, uint32_t second_off) {
     constexpr uint32_t kMat = 2 * T * T * 1024;
     for (uint32_t q = threadIdx.x; q < kMat / 16; q += blockDim.x) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + q * 16), "l"(t.tab + td.mat_off + q * 16) : "memory");
-        if (with_pre)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + kMat + q * 16), "l"(t.tab + td.pre_off + q * 16) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + q * 16), "l"(t.tab + first_off + q * 16) : "memory");
+        if (second_off)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(t.u_u32 + kMat + q * 16), "l"(t.tab + second_off + q * 16) : "memory");
     }
     tc5_stage_commit();
     tc5_stage_wait();
@@ -355,14 +372,15 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
     for (int i = 0; i < T; i++) {
         int c[32];
         tc5_load(t, 32 * i, c);
-        tc5_sweep<F, true>(st[i], c, kp + i * kTc5KBytes);
+        tc5_sweep<F, true, (T > 4)>(st[i], c, kp + i * kTc5KBytes);
     }
 }
 
 template <class F, int T, int ALPHA>
 __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc& d, const TcDesc& td, Tc5Tile& t) {
     static_assert(ALPHA == 5 || ALPHA == 17, "variant 7: alpha 5 or 17");
-    static_assert(T >= 2 && T <= 4, "variant 7: a tile's 128 TMEM columns hold T <= 4 output values");
+    static_assert(T >= 2 && T <= 5, "variant 7: widths 2..5 (a tile owns 32 T of the SM's 512 TMEM columns)");
+    constexpr bool kBoth = tc5_both_matrices(T);
     constexpr uint32_t N = T - 1, kRoundK = T * kTc5KBytes, kStack = 2 * T * 1024, kRoundPart = N * kTc5Tab + kStack;
     // A slots of the partial rounds
     constexpr uint32_t kY0 = 0, kY1 = kTc5Wide, kLane = 2 * kTc5Wide;
@@ -377,11 +395,17 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
     }
     const uint32_t half = d.half_full, rp = d.partial;
     const unsigned char* kp = t.tab + td.k_off;
-    const uint32_t mat_u32 = t.u_u32, pre_u32 = t.u_u32 + T * kStack;
+    // on entry U holds M (and M_pre behind it where both fit)
+    const uint32_t mat_u32 = t.u_u32, pre_u32 = kBoth ? t.u_u32 + T * kStack : t.u_u32;
 
 #pragma unroll 1
     for (uint32_t r = 0; r < half; r++) {
-        tc5_full_round<F, T, ALPHA>(st, (r + 1 == half && rp) ? pre_u32 : mat_u32, kp, t);
+        const bool pre = r + 1 == half && rp;
+        if (!kBoth && pre) {
+            __syncthreads();   // every tile is through with M
+            tc5_load_matrices<T>(t, td.pre_off, 0);
+        }
+        tc5_full_round<F, T, ALPHA>(st, pre ? pre_u32 : mat_u32, kp, t);
         kp += kRoundK;
     }
 
@@ -503,7 +527,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
         }
         // all tiles are through with the staging buffers: the matrices return to U
         __syncthreads();
-        tc5_load_matrices<T>(t, td, true);
+        tc5_load_matrices<T>(t, td.mat_off, kBoth ? td.pre_off : 0);
     }
 
 #pragma unroll 1

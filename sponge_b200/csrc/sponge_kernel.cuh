@@ -93,9 +93,9 @@ __device__ __forceinline__ void permute(uint32_t (&st)[T][8], const PermDesc& d)
 #define PSD_TC_BLOCK 512
 #endif
 // Variant 7: whole 128-sponge tiles; a tile owns 32 T of the SM's 512 TMEM columns, so five tiles (96 registers per thread)
-// up to T = 3 and four (128 registers) at T = 4.
+// up to T = 3, four (128 registers) at T = 4, three (168 registers) at T = 5.
 #ifndef PSD_TC5_BLOCK
-#define PSD_TC5_BLOCK(T) ((T) <= 3 ? 640 : 512)
+#define PSD_TC5_BLOCK(T) ((T) <= 3 ? 640 : (T) == 4 ? 512 : 384)
 #endif
 #define PSD_SMEM_BLOCK(T, VARIANT) ((VARIANT) == 6 ? PSD_TC_BLOCK : (VARIANT) == 7 ? PSD_TC5_BLOCK(T) : (VARIANT) == 5 ? 512 : 448)
 #define PSD_SMEM_BLOCKS(VARIANT) ((VARIANT) >= 5 ? 1 : 2)
@@ -212,7 +212,7 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         // the dense matrices into U; ends with a block-wide barrier behind a proxy fence (covers the small tables, the
         // mbarriers and the TMEM address as well)
-        tc5_load_matrices<T>(tile, a.tc, a.d.partial != 0);
+        tc5_load_matrices<T>(tile, a.tc.mat_off, (tc5_both_matrices(T) && a.d.partial != 0) ? a.tc.pre_off : 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         tile.tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0) + tl * 32 * T;
     }

@@ -92,14 +92,17 @@ bool tc_bounds_ok(const HostField& f, uint32_t t, std::string* why, uint32_t lay
         if (why) *why = m;
         return false;
     };
-    if (t < 2 || t > (layout == 1 ? 4u : 5u)) return no(layout == 1 ? "width outside [2,4]" : "width outside [2,5]");
+    if (t < 2 || t > 5) return no("width outside [2,5]");
     // column sums, in units of 32 products of two bytes.  Layout 0: at most t + 1 values of 32 bytes (the second row 0 of
     // a pair of partial rounds) plus one constant byte.  Layout 1: an S-box output is 64 bytes (two units); a full round
     // sums t of them, the second row 0 two of them and t - 1 lanes; the constant is added after the pair-combine.
     // Pair-combining needs sum * 257 < 2^32.
+    // At t = 5 the full rounds' sums (ten units) are combined in 64 bits; they only have to fit the s32 accumulators.
     const uint64_t units = layout == 1 ? (2 * t > t + 3 ? 2 * t : t + 3) : t + 1;
     const uint64_t colmax = 32ull * units * 255 * 255 + (layout == 1 ? 0 : 255);
-    if (colmax * 257 >= (1ull << 32)) return no("column sums too large for the pair-combine");
+    const uint64_t pair_units = (layout == 1 && t > 4) ? t + 3 : units;
+    if ((32ull * pair_units * 255 * 255 + (layout == 1 ? 0 : 255)) * 257 >= (1ull << 32)) return no("column sums too large for the pair-combine");
+    if (colmax >= (1ull << 31)) return no("column sums do not fit the accumulators");
     // sweep input V < colmax * 256^32 * 256/255 (+ K' < p in layout 1); result (V + m p) / 2^32 < V / 2^32 + p must stay
     // below 2^256 and, for the lazy S-box (BN254), inside its operand range 2 a + p < 2^256 with the output below 2^256
     long double p = 0;
@@ -261,7 +264,7 @@ void host_mont_row(const HostField& f, const uint32_t* v, uint32_t* out8) {
 }
 }  // namespace
 
-void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms, const uint8_t* kbytes, uint32_t* out8) {
+void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms, const uint8_t* kbytes, uint32_t* out8, bool big) {
     uint64_t col[32] = {0};
     for (uint32_t j = 0; j < n_terms; j++) {
         const Tc5HostTerm& t = terms[j];
@@ -273,7 +276,7 @@ void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms
     }
     // the device pair-combines columns in 32 bits: the sums must leave room for that
     for (int c = 0; c < 32; c++)
-        if (col[c] * 257 >= (1ull << 32)) {
+        if (big ? col[c] >= (1ull << 31) : col[c] * 257 >= (1ull << 32)) {
             for (int l = 0; l < 8; l++) out8[l] = 0xdeadbeefu;
             return;
         }

@@ -14,7 +14,7 @@ namespace psd {
 // layout 0: every table in mma.sync.m16n8k32 B-fragment order, additive constants as accumulator start values
 // (variant 6).  layout 1: tables as B operands of tcgen05.mma in the K-major no-swizzle core-matrix order
 // ([k / 16][column][k % 16]); the constants that multiply an S-box output have 64 rows (the operand is the unreduced
-// product) and are stacked along N by operand; additive constants as eight 32-bit limbs (variant 7, width <= 4).
+// product) and are stacked along N by operand; additive constants as eight 32-bit limbs (variant 7).
 void build_tc_tables(const HostField& f, uint32_t t, uint32_t full_rounds, uint32_t partial_rounds,
                      const std::vector<Fe>& ark_mont, const std::vector<Fe>& mds_mont, TcDesc& td,
                      std::vector<uint8_t>& img, uint32_t layout = 0);
@@ -38,6 +38,8 @@ struct Tc5HostTerm {
     const uint8_t* table;
     uint32_t stack, block;
 };
-void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms, const uint8_t* kbytes, uint32_t* out8);
+// big: the sums are combined in 64 bits (the full rounds at t = 5); otherwise they must leave room for the 32-bit pair-combine
+void tc5_host_row(const HostField& f, const Tc5HostTerm* terms, uint32_t n_terms, const uint8_t* kbytes, uint32_t* out8,
+                  bool big = false);
 
 }  // namespace psd

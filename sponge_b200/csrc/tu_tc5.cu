@@ -27,5 +27,6 @@ PSD_REG_TC5(3, 5)
 PSD_REG_TC5(3, 17)
 PSD_REG_TC5(2, 5)
 PSD_REG_TC5(4, 5)
+PSD_REG_TC5(5, 5)
 
 }  // namespace psd

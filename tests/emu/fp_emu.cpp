@@ -442,7 +442,7 @@ static void emu_perm_tc5_one(uint32_t (&st)[T][8], const PermDesc& d, const TcDe
         for (int i = 0; i < T; i++) {
             Tc5HostTerm terms[T];
             for (int j = 0; j < T; j++) terms[j] = Tc5HostTerm{y[j], 64, mat + j * kStack, (uint32_t)T, (uint32_t)i};
-            tc5_host_row(hf, terms, T, kp + i * kb, st[i]);
+            tc5_host_row(hf, terms, T, kp + i * kb, st[i], T > 4);
         }
         kp += T * kb;
     };
@@ -580,12 +580,14 @@ extern "C" int emu_permute_tc_layout(int field, uint32_t rate, uint32_t capacity
                 case 2: return emu_perm_tc5_a<Bn254Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
                 case 3: return emu_perm_tc5_a<Bn254Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
                 case 4: return emu_perm_tc5_a<Bn254Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+                case 5: return emu_perm_tc5_a<Bn254Fr, 5>(alpha, d, td, tab.data(), *hf, states, n);
             }
         } else {
             switch (t) {
                 case 2: return emu_perm_tc5_a<Bls12381Fr, 2>(alpha, d, td, tab.data(), *hf, states, n);
                 case 3: return emu_perm_tc5_a<Bls12381Fr, 3>(alpha, d, td, tab.data(), *hf, states, n);
                 case 4: return emu_perm_tc5_a<Bls12381Fr, 4>(alpha, d, td, tab.data(), *hf, states, n);
+                case 5: return emu_perm_tc5_a<Bls12381Fr, 5>(alpha, d, td, tab.data(), *hf, states, n);
             }
         }
         return -1;

@@ -156,7 +156,7 @@ def test_fast_variants_equal_dense_on_every_element_of_the_full_batch(S, ref, na
         x = torch.empty((n * width, 4), dtype=torch.int64, device="cuda:0")
         ctx.synth_fill_dev(x.data_ptr(), n * width, 0x5D0)
         outs = []
-        for variant in ((7, 6, 0) if t <= 4 else (6, 5, 0)):
+        for variant in (7, 6, 0):
             ctx.set_variant(variant)
             assert ctx.active_variant() == variant
             if absorb == 0:

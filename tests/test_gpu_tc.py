@@ -24,8 +24,8 @@ def make(ref, name):
 
 
 def has_variant7(oc):
-    """Variant 7 (tcgen05 / TMEM form of the same contraction) is built for widths up to 4."""
-    return oc.rate + oc.capacity <= 4
+    """Variant 7 (tcgen05 / TMEM form of the same contraction) is built for the same widths and exponents as variant 6."""
+    return oc.rate + oc.capacity <= 5
 
 
 @pytest.mark.parametrize("variant", [6, 7])
