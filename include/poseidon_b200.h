@@ -296,8 +296,12 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 6 = integer S-box + the whole linear layer on the tensor cores: every product by a round constant is a
  *     u8 x u8 -> s32 matrix product against the constant's 32 x 32 byte-digit table (mma.sync.m16n8k32),
  *     followed by one carry sweep and one 32-bit Montgomery row per output value (t = 2..5, alpha 5 or
- *     17, both fields).  The default for BN254 Fr; BLS12-381 Fr defaults to 5 -> 3 (variant 6 measured
- *     slower there).  Lock-step calls only: ragged batches run the next variant down.
+ *     17, both fields).  Lock-step calls only: ragged batches run the next variant down.
+ * 7 = the same contraction through tcgen05.mma.kind::i8 with the accumulators in tensor memory, and with
+ *     every Montgomery reduction of the S-box done the same way (a reduction is a product by constants):
+ *     the integer pipe only computes unreduced squares and products.  t = 2..5, alpha 5 or 17, both
+ *     fields; the default.  Lock-step calls only.  Where it has no kernel the request degrades to 6 (BN254)
+ *     or to the integer variants (BLS12-381, where 6 measured slower than 3).
  * A request is served by the best kernel <= it that exists for the context's field, width and home of
  * constants; psd_ctx_active_variant / psd_ctx_describe report what a launch really runs.
  *
@@ -308,9 +312,10 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * the bank, then falls back to the shared-memory form, which any number of parameter sets can use at
  * once -- so creating a context never fails for lack of constant-bank space and a second parameter set
  * of the same shape runs the same algorithm as the first (measured within a few percent; the t = 5
- * variant-5 tables, 100 KiB, exist in the shared-memory form only).  Variant 6 keeps its tables (1 KiB per
- * constant, 250 KiB for t = 3) in global memory, where the L1/L2 caches serve them, and stages only the
- * round-0 constants; any number of parameter sets can use it at once. */
+ * variant-5 tables, 100 KiB, exist in the shared-memory form only).  Variants 6 and 7 keep their tables (1 or
+ * 2 KiB per constant, 250 / 560 KiB for t = 3) in global memory, where the L1/L2 caches serve them (variant 7
+ * stages a pair of rounds' tables into shared memory one pair ahead), and stage only the round-0
+ * constants; any number of parameter sets can use them at once. */
 psd_status psd_ctx_set_variant(psd_ctx* ctx, int variant);
 psd_status psd_ctx_active_variant(const psd_ctx* ctx, int* variant);
 typedef enum psd_constants_home { PSD_CONSTANTS_BANK = 0, PSD_CONSTANTS_SHARED = 1 } psd_constants_home;
