@@ -297,6 +297,12 @@ def executed_work(ctx, name, log_n, perms_per_step_gpu, ms_per_step, clocks):
             out["heavy_pipe_frac"] = heavy * warp_perms / cycles
             out["w_exec_imul_per_perm"] = per.get("imad_wide", 0) + per.get("imad_hi", 0) + per.get("imad", 0)
             out["fp64_inst_per_perm"] = per.get("fp64", 0)
+            if m.group(4) == "7" and per.get("mma"):
+                # tcgen05.mma instructions (each serves a 128-sponge tile) and the share of the time the tensor pipe needs
+                # for them at the 67 cycles per instruction per SM that tools/tc5_bw.cu measured for N <= 128
+                mma_per_perm = per["mma"] / 32.0
+                out["tcgen05_mma_per_perm"] = mma_per_perm
+                out["tensor_pipe_frac_at_67_cycles_per_mma"] = mma_per_perm * perms_per_step_gpu * 67.0 / (sm_count * cycles)
         if crec.get("workload") == name and crec.get("log_n") == log_n and fresh:
             traffic = crec.get("dram_bytes_per_launch")
     return out, traffic

@@ -30,8 +30,8 @@ def classify(op):
         return "imad_other"
     if op.startswith(("DFMA", "DADD", "DMUL")):
         return "fp64"
-    if op.startswith(("IMMA", "HMMA", "DMMA")):
-        return "mma"
+    if op.startswith(("IMMA", "HMMA", "DMMA")) or (op.startswith("UTC") and "MMA" in op):
+        return "mma"   # warp-level mma.sync, or tcgen05.mma (one warp-level execution = one instruction for the whole tile)
     if op.startswith(("LDS", "STS", "LDSM")):
         return "shared_ldst"
     if op.startswith(("LDG", "STG", "LDL", "STL", "LD.", "ST.")):
