@@ -3,14 +3,14 @@
 // memory and the accumulators in TMEM -- and, because a Montgomery reduction is itself a product by constants
 // (z mod p = sum_k byte_k(z) (256^k mod p)), every reduction of the S-box as well.
 //
-// A thread block is four TILES of 128 sponges (4 warps each).  Per tile
+// A thread block is three to five TILES of 128 sponges (4 warps each; 5 up to t = 3, 4 at t = 4, 3 at t = 5).  Per tile
 //   * every thread writes the bytes of a value ONCE into an A slot of the tile (K-major core-matrix layout: 16-byte chunk c
 //     of row r at c * 2048 + r * 16): 32 bytes for a state element, 64 bytes for an UNREDUCED product of two elements;
 //   * ONE thread issues the MMAs of a step (M = 128 sponges, K = 32 bytes per instruction, N = 32 columns per constant; the
 //     constants that multiply the same value are stacked along N, so one instruction pair serves row 0 AND all lanes) and
 //     commits them to the tile's mbarrier; measured on B200: 67 cycles per instruction per SM for every N <= 128, so the
 //     instruction COUNT is what the layout minimises;
-//   * the accumulators live in the tile's 128 TMEM columns, and tcgen05.ld.32x32b hands thread r the 32 column sums of ITS
+//   * the accumulators live in the tile's 32 t TMEM columns, and tcgen05.ld.32x32b hands thread r the 32 column sums of ITS
 //     OWN row -- no exchange, no fragments;
 //   * the sweep (pair-combine, carry add, one 32-bit Montgomery row) turns 32 column sums into a value < p + 2^249.
 // The S-box x^5 is then: square (36 wide multiplies, unreduced) -> tensor-core reduction -> square -> reduction -> product
