@@ -580,6 +580,16 @@ psd_status run_staged(psd_ctx* ctx, const StagedCall& c, Fill fill) {
     uint64_t chunk = std::max<uint64_t>((256ull << 20) / per, std::min<uint64_t>(1ull << 16, (512ull << 20) / per));
     chunk = std::max<uint64_t>(chunk, 1);
     chunk = std::min<uint64_t>(chunk, 1ull << chunk_log2);
+    // Whole waves: a chunk that is a multiple of (SMs x sponges per block) leaves no partly filled last wave behind every
+    // launch (2^17 sponges are 1.38 waves of variant 7's 640-sponge blocks).
+    static const int whole_waves = env_int("PSD_STAGE_WAVES", 1);
+    if (whole_waves) {
+        const Resolved r = resolve_kernel(ctx);
+        if (r.k) {
+            const uint64_t wave = (uint64_t)sponge_cfg(ctx, r.k, chunk).block * (uint64_t)std::max(1, ctx->sm_count);
+            if (chunk > wave) chunk = std::max<uint64_t>(1, (chunk + wave / 2) / wave) * wave;
+        }
+    }
     chunk = std::min<uint64_t>(chunk, end - begin);
     psd_status st = ensure_staging(ctx, std::max<size_t>(chunk * in_per, 16), c.in_place ? 0 : std::max<size_t>(chunk * out_per, 16));
     if (st != PSD_OK) return st;
