@@ -66,10 +66,10 @@ PSD_HD constexpr uint32_t tc5_smem_bytes(uint32_t t, uint32_t tiles) {
 
 struct Tc5Tile {
     uint32_t tmem;            // TMEM address of this tile's column 0 (lane field 0)
-    uint32_t a_u32;           // shared-memory address of the tile's A slots
-    uint32_t stage_u32;       // ... of the tile's staging buffer (inside U)
-    uint32_t small_u32;       // ... of the block's small tables
-    uint32_t u_u32;           // ... of U
+    uint32_t a_q;             // shared-memory address / 16 of the tile's A slots
+    uint32_t stage_u32;       // shared-memory address of the tile's staging buffer (inside U)
+    uint32_t small_q;         // address / 16 of the block's small tables
+    uint32_t u_u32;           // address of U
     // Two mbarriers per tile: a step commits twice (row 0 first, the lanes behind it), and a waiter may be at most one
     // phase behind an mbarrier, so the two completions must not share one.
     uint32_t mbar_u32[2];
@@ -81,24 +81,30 @@ struct Tc5Tile {
     bool leader_warp;         // warp-uniform: the tile's first warp, one elected thread of which issues the tile's MMAs
 };
 
-__device__ __forceinline__ uint64_t tc5_desc(uint32_t saddr, uint32_t lbo) {
+// Shared-memory operand addresses travel as 16-byte units (`q` = address / 16: every operand here is 16-byte aligned and the
+// shared window is below 256 KiB), so a descriptor is one 32-bit add away from its region's base: the issuing warp carries
+// 15 % more instructions than its three siblings, and they wait for it at every step.
+__device__ __forceinline__ uint64_t tc5_desc(uint32_t q, uint32_t lbo) {
     // K-major, no swizzle, version 1; 8-row groups 128 bytes apart; lbo = bytes between the two 16-byte K chunks
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
+    const uint32_t lo = q + ((lbo >> 4) << 16), hi = (128u >> 4) | (1u << 14);
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
 }
 // u8 x u8 -> s32, M 128, N n
 __device__ __forceinline__ constexpr uint32_t tc5_idesc(uint32_t n) { return (2u << 4) | ((n >> 3) << 17) | ((128u >> 4) << 24); }
 
-// D[columns d .. d + 32 blocks - 1] (+)= A (128 rows x 32 bytes at a_u32) x B^T (32 blocks columns x 32 bytes at b_u32)
-__device__ __forceinline__ void tc5_mma(uint32_t d, uint32_t a_u32, uint32_t b_u32, uint32_t blocks, bool accumulate) {
-    const uint64_t da = tc5_desc(a_u32, kTc5Chunk), db = tc5_desc(b_u32, blocks * 512);
+// D[columns d .. d + 32 blocks - 1] (+)= A (128 rows x 32 bytes at 16 a_q) x B^T (32 blocks columns x 32 bytes at 16 b_q)
+__device__ __forceinline__ void tc5_mma(uint32_t d, uint32_t a_q, uint32_t b_q, uint32_t blocks, bool accumulate) {
+    const uint64_t da = tc5_desc(a_q, kTc5Chunk), db = tc5_desc(b_q, blocks * 512);
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
                  ::"r"(d), "l"(da), "l"(db), "r"(tc5_idesc(32 * blocks)), "r"((uint32_t)accumulate), "r"(0u) : "memory");
 }
 // a 64-byte value against a stack of `blocks` 64-row tables: two instructions
-__device__ __forceinline__ void tc5_mma_wide(uint32_t d, uint32_t a_u32, uint32_t b_u32, uint32_t blocks, bool accumulate) {
-    tc5_mma(d, a_u32, b_u32, blocks, accumulate);
-    tc5_mma(d, a_u32 + 2 * kTc5Chunk, b_u32 + 2 * blocks * 512, blocks, true);
+__device__ __forceinline__ void tc5_mma_wide(uint32_t d, uint32_t a_q, uint32_t b_q, uint32_t blocks, bool accumulate) {
+    tc5_mma(d, a_q, b_q, blocks, accumulate);
+    tc5_mma(d, a_q + 2 * kTc5Chunk / 16, b_q + 2 * blocks * 512 / 16, blocks, true);
 }
 __device__ __forceinline__ void tc5_commit(const Tc5Tile& t, int which) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(t.mbar_u32[which]) : "memory");
@@ -279,7 +285,7 @@ __device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, T
         tc5_store_wide(t, off, w);
         tc5_step_begin(t);
         if (t.leader_warp && tc5_elect()) {
-            tc5_mma_wide(t.tmem, t.a_u32 + off, t.small_u32 + 3 * 1024, 1, false);
+            tc5_mma_wide(t.tmem, t.a_q + off / 16, t.small_q + 3 * 1024 / 16, 1, false);
             tc5_commit(t, 0);
         }
         if (q == 0) lanes();
@@ -293,9 +299,9 @@ __device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, T
 }
 
 // One full round: T S-boxes into the wide slots 0..T-1, 2 T instructions (S-box output j against column j of the matrix,
-// all rows stacked), T sweeps.  mat_u32: the matrix's stacks in U, kp: the T additive constants of the round.
+// all rows stacked), T sweeps.  mat_q: the matrix's stacks in U (address / 16), kp: the T additive constants of the round.
 template <class F, int T, int ALPHA>
-__device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t mat_u32, const unsigned char* kp, Tc5Tile& t) {
+__device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t mat_q, const unsigned char* kp, Tc5Tile& t) {
     uint32_t y[T][8];
 #pragma unroll
     for (int j = 0; j < T; j++)
@@ -312,7 +318,7 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
         tc5_step_begin(t);
         if (t.leader_warp && tc5_elect()) {
 #pragma unroll
-            for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem + 32 * j, t.a_u32 + j * kTc5Wide, t.small_u32 + 3 * 1024, 1, false);
+            for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem + 32 * j, t.a_q + j * kTc5Wide / 16, t.small_q + 3 * 1024 / 16, 1, false);
             tc5_commit(t, 0);
         }
         tc5_wait(t, 0);
@@ -332,7 +338,7 @@ __device__ __forceinline__ void tc5_full_round(uint32_t (&st)[T][8], uint32_t ma
     tc5_step_begin(t);
     if (t.leader_warp && tc5_elect()) {
 #pragma unroll
-        for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem, t.a_u32 + j * kTc5Wide, mat_u32 + j * 2 * T * 1024, T, j > 0);
+        for (int j = 0; j < T; j++) tc5_mma_wide(t.tmem, t.a_q + j * kTc5Wide / 16, mat_q + j * 2 * T * 1024 / 16, T, j > 0);
         tc5_commit(t, 0);
     }
     tc5_wait(t, 0);
@@ -353,8 +359,11 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
     // A slots of the partial rounds
     constexpr uint32_t kY0 = 0, kY1 = kTc5Wide, kLane = 2 * kTc5Wide;
     // staging: w(i), the stack (c_q, v(i)), then -- one contiguous piece of the image -- w(i+1) and the stack (M00, v(i+1))
-    const uint32_t sWa = t.stage_u32, sBy0 = sWa + N * kTc5Tab, sWb = sBy0 + kStack, sBy1 = sWb + N * kTc5Tab;
-    const uint32_t m00_u32 = t.small_u32, ident_u32 = t.small_u32 + 2 * 1024;
+    const uint32_t sWa = t.stage_u32, sBy0 = sWa + N * kTc5Tab, sWb = sBy0 + kStack;
+    // the same as MMA operands (address / 16), and the A slots
+    const uint32_t qWa = sWa >> 4, qBy0 = sBy0 >> 4, qWb = sWb >> 4, qBy1 = qWb + N * kTc5Tab / 16;
+    const uint32_t qM00 = t.small_q, qIdent = t.small_q + 2 * 1024 / 16;
+    const uint32_t qY0 = t.a_q + kY0 / 16, qY1 = t.a_q + kY1 / 16, qLane = t.a_q + kLane / 16;
 #pragma unroll
     for (int j = 0; j < T; j++) {
         uint32_t c[8];
@@ -364,7 +373,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
     const uint32_t half = d.half_full, rp = d.partial;
     const unsigned char* kp = t.tab + td.k_off;
     // on entry U holds M (and M_pre behind it where both fit)
-    const uint32_t mat_u32 = t.u_u32, pre_u32 = kBoth ? t.u_u32 + T * kStack : t.u_u32;
+    const uint32_t mat_q = t.u_u32 >> 4, pre_q = kBoth ? mat_q + T * kStack / 16 : mat_q;
 
 #pragma unroll 1
     for (uint32_t r = 0; r < half; r++) {
@@ -373,7 +382,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
             __syncthreads();   // every tile is through with M
             tc5_load_matrices<T>(t, td.pre_off, 0);
         }
-        tc5_full_round<F, T, ALPHA>(st, pre ? pre_u32 : mat_u32, kp, t);
+        tc5_full_round<F, T, ALPHA>(st, pre ? pre_q : mat_q, kp, t);
         kp += kRoundK;
     }
 
@@ -400,12 +409,12 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
             tc5_stage_wait();
             tc5_step_begin(t);
             if (t.leader_warp && tc5_elect()) {
-                tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy1, T, false);
+                tc5_mma_wide(t.tmem, qY0, qBy1, T, false);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWb + (j - 1) * kTc5Tab, 1, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, qLane + (j - 1) * kTc5Narrow / 16, qWb + (j - 1) * kTc5Tab / 16, 1, true);
                 tc5_commit(t, 0);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, t.a_u32 + kLane + (j - 1) * kTc5Narrow, ident_u32, 1, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, qLane + (j - 1) * kTc5Narrow / 16, qIdent, 1, true);
                 tc5_commit(t, 1);
             }
             tc5_wait(t, 0);
@@ -440,9 +449,9 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
             tc5_stage_wait();
             tc5_step_begin(t);
             if (t.leader_warp && tc5_elect()) {
-                tc5_mma_wide(t.tmem, t.a_u32 + kY0, m00_u32, 1, false);
+                tc5_mma_wide(t.tmem, qY0, qM00, 1, false);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWa + (j - 1) * kTc5Tab, 1, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, qLane + (j - 1) * kTc5Narrow / 16, qWa + (j - 1) * kTc5Tab / 16, 1, true);
                 tc5_commit(t, 0);
             }
             tc5_wait(t, 0);
@@ -456,13 +465,13 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
             tc5_sbox_slot<F, T, ALPHA, false>(st[0], kY1, t);
             tc5_step_begin(t);
             if (t.leader_warp && tc5_elect()) {
-                tc5_mma_wide(t.tmem, t.a_u32 + kY1, sBy1, T, false);
-                tc5_mma_wide(t.tmem, t.a_u32 + kY0, sBy0, T, true);
+                tc5_mma_wide(t.tmem, qY1, qBy1, T, false);
+                tc5_mma_wide(t.tmem, qY0, qBy0, T, true);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t.tmem, t.a_u32 + kLane + (j - 1) * kTc5Narrow, sWb + (j - 1) * kTc5Tab, 1, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem, qLane + (j - 1) * kTc5Narrow / 16, qWb + (j - 1) * kTc5Tab / 16, 1, true);
                 tc5_commit(t, 0);
 #pragma unroll
-                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, t.a_u32 + kLane + (j - 1) * kTc5Narrow, ident_u32, 1, true);
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, qLane + (j - 1) * kTc5Narrow / 16, qIdent, 1, true);
                 tc5_commit(t, 1);
             }
             tc5_wait(t, 0);
@@ -500,7 +509,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
 
 #pragma unroll 1
     for (uint32_t r = half + rp; r < d.total; r++) {
-        tc5_full_round<F, T, ALPHA>(st, mat_u32, kp, t);
+        tc5_full_round<F, T, ALPHA>(st, mat_q, kp, t);
         kp += kRoundK;
     }
 

@@ -183,8 +183,8 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
         tile.bar_id = 1 + (int)tl;
         tile.tab = a.tc_tab;
         tile.a_ptr = a0 + tl * tc5_a_bytes(T);
-        tile.a_u32 = (uint32_t)__cvta_generic_to_shared(tile.a_ptr);
-        tile.small_u32 = (uint32_t)__cvta_generic_to_shared(base);
+        tile.a_q = (uint32_t)__cvta_generic_to_shared(tile.a_ptr) >> 4;
+        tile.small_q = (uint32_t)__cvta_generic_to_shared(base) >> 4;
         tile.u_u32 = (uint32_t)__cvta_generic_to_shared(u0);
         tile.stage_u32 = tile.u_u32 + tl * tc5_stage_bytes(T);
         tile.mbar_u32[0] = (uint32_t)__cvta_generic_to_shared(bars + tl * 16);
