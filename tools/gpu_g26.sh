@@ -1,5 +1,5 @@
 set -x
-O=gpurun_out/g25
+O=gpurun_out/g26
 mkdir -p $O
 timeout 300 python -m pytest tests/test_gpu_tc.py -m gpu -x -q -k "permute and bn254_t3 and 7" > $O/pytest_first.log 2>&1; rc=$?; echo "rc=$rc" >> $O/pytest_first.log; tail -15 $O/pytest_first.log
 if [ $rc -ne 0 ]; then exit 0; fi
