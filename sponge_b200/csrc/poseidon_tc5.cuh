@@ -196,20 +196,8 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
         for (int k = 1; k < 8; k++) ys[k] = __funnelshift_l(Y[k - 1], Y[k], 16);
         ys[8] = Y[7] >> 16;
     }
-    uint32_t v[9];
-    asm("add.cc.u32 %0, %9, %18;\n\t"
-        "addc.cc.u32 %1, %10, %19;\n\t"
-        "addc.cc.u32 %2, %11, %20;\n\t"
-        "addc.cc.u32 %3, %12, %21;\n\t"
-        "addc.cc.u32 %4, %13, %22;\n\t"
-        "addc.cc.u32 %5, %14, %23;\n\t"
-        "addc.cc.u32 %6, %15, %24;\n\t"
-        "addc.cc.u32 %7, %16, %25;\n\t"
-        "addc.u32 %8, %17, 0;"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8])
-        : "r"(X[0]), "r"(X[1]), "r"(X[2]), "r"(X[3]), "r"(X[4]), "r"(X[5]), "r"(X[6]), "r"(X[7]), "r"(ys[8]), "r"(ys[0]),
-          "r"(ys[1]), "r"(ys[2]), "r"(ys[3]), "r"(ys[4]), "r"(ys[5]), "r"(ys[6]), "r"(ys[7]));
     if (HASK) {
+        // the additive constant joins the shifted half: ys += K (ys[8] stays small: it only takes the carry)
         const uint4 k0 = __ldg(reinterpret_cast<const uint4*>(kptr)), k1 = __ldg(reinterpret_cast<const uint4*>(kptr) + 1);
         asm("add.cc.u32 %0, %0, %9;\n\t"
             "addc.cc.u32 %1, %1, %10;\n\t"
@@ -220,16 +208,32 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
             "addc.cc.u32 %6, %6, %15;\n\t"
             "addc.cc.u32 %7, %7, %16;\n\t"
             "addc.u32 %8, %8, 0;"
-            : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8])
+            : "+r"(ys[0]), "+r"(ys[1]), "+r"(ys[2]), "+r"(ys[3]), "+r"(ys[4]), "+r"(ys[5]), "+r"(ys[6]), "+r"(ys[7]), "+r"(ys[8])
             : "r"(k0.x), "r"(k0.y), "r"(k0.z), "r"(k0.w), "r"(k1.x), "r"(k1.y), "r"(k1.z), "r"(k1.w));
     }
-    const uint32_t m = v[0] * np0<F>();
-    uint32_t c8 = 0;
-    mad4(v, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, c8);
-    uint32_t x[8] = {v[1], v[2], v[3], v[4], v[5], v[6], v[7], v[8] + c8};
-    mad4_nc(x, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
-#pragma unroll
-    for (int k = 0; k < 8; k++) out[k] = x[k];
+    // (X + ys + m p) / 2^32 without ever forming X + ys: the Montgomery row's even products accumulate onto X's register
+    // pairs, its odd products onto the pairs (ys1, ys2), (ys3, ys4), .. -- both are pairs as IMAD.WIDE wants them -- and one
+    // 9-limb add joins the two halves one limb apart.  (Accumulating both product chains onto ONE sum needs the sum in two
+    // pairings, i.e. eight register moves per sweep.)  Limb 0 of the total is zero by the choice of m: its add only makes the
+    // carry.
+    const uint32_t m = (X[0] + ys[0]) * np0<F>();
+    uint32_t ca = 0;
+    mad4(X, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, ca);
+    mad4_nc(ys + 1, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    uint32_t zero;
+    asm("add.cc.u32 %8, %9, %18;\n\t"
+        "addc.cc.u32 %0, %10, %19;\n\t"
+        "addc.cc.u32 %1, %11, %20;\n\t"
+        "addc.cc.u32 %2, %12, %21;\n\t"
+        "addc.cc.u32 %3, %13, %22;\n\t"
+        "addc.cc.u32 %4, %14, %23;\n\t"
+        "addc.cc.u32 %5, %15, %24;\n\t"
+        "addc.cc.u32 %6, %16, %25;\n\t"
+        "addc.u32 %7, %17, %26;"
+        : "=r"(out[0]), "=r"(out[1]), "=r"(out[2]), "=r"(out[3]), "=r"(out[4]), "=r"(out[5]), "=r"(out[6]), "=r"(out[7]), "=r"(zero)
+        : "r"(X[0]), "r"(X[1]), "r"(X[2]), "r"(X[3]), "r"(X[4]), "r"(X[5]), "r"(X[6]), "r"(X[7]), "r"(ca), "r"(ys[0]), "r"(ys[1]),
+          "r"(ys[2]), "r"(ys[3]), "r"(ys[4]), "r"(ys[5]), "r"(ys[6]), "r"(ys[7]), "r"(ys[8]));
+    (void)zero;
 }
 
 // `bytes` of tables, global -> shared at dst_u32, by cp.async (no registers held), spread over the tile's threads
