@@ -262,27 +262,25 @@ __device__ __forceinline__ void tc5_load_matrices(const Tc5Tile& t, uint32_t fir
 }
 
 // the S-box of ONE value: x -> the unreduced 64 bytes of x^ALPHA in the wide slot at `off`.
-// SHADOW: the lane columns of the previous step (tile columns 32 j, complete) are swept and written back to their A slots
-// while the first reduction is on its way through the tensor core -- work that depends on nothing in the S-box chain.
-template <class F, int T, int ALPHA, bool SHADOW>
-__device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, Tc5Tile& t, bool lanes_pending = false,
-                                              uint32_t lane_off = 0) {
+// LANES: the lane columns of the previous step (tile columns 32 j, complete) are swept and written back to their A slots
+// first -- in one straight line with the first squaring, which depends on none of it, so that the compiler can fill the
+// squaring's multiplier latencies with the sweeps' ALU work (+0.5 % on C2 against doing it while the first reduction is on
+// its way through the tensor core).
+template <class F, int T, int ALPHA, bool LANES>
+__device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, Tc5Tile& t, uint32_t lane_off = 0) {
     uint32_t y[8], in[8], w[16];
-    auto lanes = [&]() {
-        if (SHADOW && lanes_pending) {
-            __syncwarp();   // behind the one-thread issue block; the TMEM loads are warp-collective
-#pragma unroll
-            for (int j = 1; j < T; j++) {
-                int c[32];
-                uint32_t lane[8];
-                tc5_load(t, 32 * j, c);
-                tc5_sweep<F, false>(lane, c, nullptr);
-                tc5_store_a(t, lane_off + (j - 1) * kTc5Narrow, lane);
-            }
-        }
-    };
 #pragma unroll
     for (int k = 0; k < 8; k++) in[k] = y[k] = x[k];
+    if (LANES) {
+#pragma unroll
+        for (int j = 1; j < T; j++) {
+            int c[32];
+            uint32_t lane[8];
+            tc5_load(t, 32 * j, c);
+            tc5_sweep<F, false>(lane, c, nullptr);
+            tc5_store_a(t, lane_off + (j - 1) * kTc5Narrow, lane);
+        }
+    }
 #pragma unroll
     for (int q = 0; q < (ALPHA == 5 ? 2 : 4); q++) {
         sqr_wide(w, y);
@@ -292,7 +290,6 @@ __device__ __forceinline__ void tc5_sbox_slot(const uint32_t* x, uint32_t off, T
             tc5_mma_wide(t.tmem, t.a_q + off / 16, t.small_q + 3 * 1024 / 16, 1, false);
             tc5_commit(t, 0);
         }
-        if (q == 0) lanes();
         tc5_wait(t, 0);
         int c[32];
         tc5_load(t, 0, c);
@@ -406,7 +403,17 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
         tc5_stage_commit();
 #pragma unroll
         for (int j = 1; j < T; j++) tc5_store_a(t, kLane + (j - 1) * kTc5Narrow, st[j]);
-        bool lanes_pending = false;   // the last step's lane columns wait in TMEM for the next S-box's shadow
+        if (!(rp & 1)) {
+            // every pair finds the lanes as column sums in TMEM (the previous step's), the first one too: 1 s_j through the
+            // tensor core
+            tc5_step_begin(t);
+            if (t.leader_warp && tc5_elect()) {
+#pragma unroll
+                for (int j = 1; j < T; j++) tc5_mma(t.tmem + 32 * j, t.a_q + (kLane + (j - 1) * kTc5Narrow) / 16, t.small_q + 2 * 1024 / 16, 1, false);
+                tc5_commit(t, 1);
+            }
+            tc5_wait(t, 1);
+        }
         if (rp & 1) {
             // an odd number of partial rounds: the first one on its own.  y0 against the stack (M00, v): row 0 and lanes
             tc5_sbox_slot<F, T, ALPHA, false>(st[0], kY0, t);
@@ -433,7 +440,6 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
                 tc5_stage(t, sBy0, pair, kStack);
                 tc5_stage(t, sWb, part + 2 * kRoundPart, kRoundPart);
                 tc5_stage_commit();
-                lanes_pending = true;
             } else {
 #pragma unroll
                 for (int j = 1; j < T; j++) {
@@ -449,7 +455,7 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
         for (uint32_t q = 0; q < pairs; q++) {
             const bool last = q + 1 == pairs;
             // first round of the pair:  row 0 = M00 y0 + sum_j w_j(i) s_j
-            tc5_sbox_slot<F, T, ALPHA, true>(st[0], kY0, t, lanes_pending, kLane);
+            tc5_sbox_slot<F, T, ALPHA, true>(st[0], kY0, t, kLane);
             tc5_stage_wait();
             tc5_step_begin(t);
             if (t.leader_warp && tc5_elect()) {
@@ -495,12 +501,11 @@ __device__ __forceinline__ void permute_tc5(uint32_t (&st)[T][8], const PermDesc
                     tc5_sweep<F, true>(st[j], c, kp + kRoundK + j * kTc5KBytes);
                 }
             } else {
-                // the next pair's tables; its first S-box sweeps this pair's lanes in its shadow
+                // the next pair's tables; its first S-box sweeps this pair's lanes
                 tc5_stage(t, sWa, part + 2 * kRoundPart, N * kTc5Tab);
                 tc5_stage(t, sBy0, pair + kStack, kStack);
                 tc5_stage(t, sWb, part + 3 * kRoundPart, kRoundPart);
                 tc5_stage_commit();
-                lanes_pending = true;
             }
             kp += 2 * kRoundK;
             part += 2 * kRoundPart;

@@ -6,7 +6,7 @@ for last in "$@"; do :; done
 POSEIDON_B200_LIB=$PWD/altlib/lib$last.so timeout 300 python -m pytest tests/test_gpu_tc.py -m gpu -x -q -k "permute and (bn254_t3 or bn254_t5) and 7" > $O/pytest_$last.log 2>&1; echo "rc=$?" >> $O/pytest_$last.log
 for round in 1 2; do
 for n in "$@"; do
-  POSEIDON_B200_LIB=$PWD/altlib/lib$n.so timeout 300 python bench.py --workload c2 --steps 5 --warmup 3 --no-cpu --no-e2e > $O/bench_${n}_$round.json 2> $O/bench_${n}_$round.err
+  POSEIDON_B200_LIB=$PWD/altlib/lib$n.so timeout 300 python bench.py --workload ${WL:-c2} --steps 5 --warmup 3 --no-cpu --no-e2e > $O/bench_${n}_$round.json 2> $O/bench_${n}_$round.err
 done
 done
 true
