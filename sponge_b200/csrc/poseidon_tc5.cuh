@@ -218,8 +218,14 @@ __device__ __forceinline__ void tc5_sweep(uint32_t* out, const int (&c)[32], con
     // carry.
     const uint32_t m = (X[0] + ys[0]) * np0<F>();
     uint32_t ca = 0;
-    mad4(X, plimb<F, 0>(), plimb<F, 2>(), plimb<F, 4>(), plimb<F, 6>(), m, ca);
-    mad4_nc(ys + 1, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    // (redc_lo / redc_hi: BLS12-381's p0 = 1 and p1 = 2^32 - 1 turn two of the eight products into adds)
+    redc_lo<F>(X, m, ca);
+    if (F::kBits == 255) {
+        uint32_t none = 0;   // the top pair cannot carry out: ys[8] only holds a carry and m p7 < 2^63
+        redc_hi<F>(ys + 1, m, none);
+    } else {
+        mad4_nc(ys + 1, plimb<F, 1>(), plimb<F, 3>(), plimb<F, 5>(), plimb<F, 7>(), m);
+    }
     uint32_t zero;
     asm("add.cc.u32 %8, %9, %18;\n\t"
         "addc.cc.u32 %0, %10, %19;\n\t"
