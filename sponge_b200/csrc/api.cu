@@ -783,8 +783,8 @@ psd_status psd_ctx_create(const psd_params* p, int device, psd_ctx** out) {
     ctx->capacity = p->capacity;
     ctx->t = t;
     ctx->alpha = p->alpha;
-    // Default request: variant 7 (tcgen05 linear layer AND reductions; c2: 362 M perm/s against 220 M for variant 6,
-    // c5: 349 M against 169 M for variant 3).  Where variant 7 has no kernel the request degrades: BN254 to 6, then 5;
+    // Default request: variant 7 (tcgen05 linear layer AND reductions; c2: 378 M perm/s against 220 M for variant 6,
+    // c5: 380 M against 169 M for variant 3).  Where variant 7 has no kernel the request degrades: BN254 to 6, then 5;
     // BLS12-381 skips 6 (mma.sync form, S-box with full reductions: 126 M perm/s on c5, slower than the all-integer
     // variant 3) unless psd_ctx_set_variant(ctx, 6) asks for exactly that.
     ctx->variant = 7;
