@@ -137,8 +137,9 @@ psd_status psd_absorb_squeeze_bytes_batch(psd_ctx* ctx, const uint64_t* inputs, 
  * offsets has n+1 entries, offsets[0] = 0, non-decreasing; a sponge may absorb nothing) and then squeezes
  * n_squeeze elements -- what the reference's callers do when they absorb lists of differing lengths into
  * different sponges (src/poseidon/tests.rs:45-69; AbsorbWithLength, absorb.rs:82-101).  Same kernel variant
- * as the lock-step calls, in a form whose warps tolerate differing lengths; sort or bucket by length on the
- * caller's side if the lengths vary widely (a warp takes as long as its longest sponge).  outputs: n*n_squeeze
+ * as the lock-step calls, in a form that tolerates differing lengths; sort or bucket by length on the
+ * caller's side if the lengths vary widely (with the default kernel a thread block of up to 640 sponges, with
+ * the integer kernels a warp, takes as long as its longest sponge).  outputs: n*n_squeeze
  * elements.  mem = PSD_MEM_DEVICE: inputs, offsets and outputs are device pointers. */
 psd_status psd_absorb_squeeze_ragged_batch(psd_ctx* ctx, const uint64_t* inputs, const uint64_t* offsets, size_t n,
                                            uint32_t n_squeeze, uint64_t* outputs, int repr, int mem, void* stream);
@@ -300,7 +301,8 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 7 = the same contraction through tcgen05.mma.kind::i8 with the accumulators in tensor memory, and with
  *     every Montgomery reduction of the S-box done the same way (a reduction is a product by constants):
  *     the integer pipe only computes unreduced squares and products.  t = 2..5, alpha 5 or 17, both
- *     fields; the default.  Lock-step calls only.  Where it has no kernel the request degrades to 6 (BN254)
+ *     fields; the default.  Ragged batches at t = 3 and t = 5 too (the block permutes while any of its sponges
+ *     needs to).  Where it has no kernel the request degrades to 6 (BN254)
  *     or to the integer variants (BLS12-381, where 6 measured slower than 3).
  * A request is served by the best kernel <= it that exists for the context's field, width and home of
  * constants; psd_ctx_active_variant / psd_ctx_describe report what a launch really runs.

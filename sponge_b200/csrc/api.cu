@@ -397,8 +397,9 @@ Resolved resolve_kernel(const psd_ctx* ctx, int ragged = 0) {
     Resolved r;
     // variant 6 uses warp-collective instructions, so it serves the lock-step calls only; ragged batches take
     // the next variant down
-    if (ctx->variant >= 7 && !ragged && ctx->pl_tc && ctx->pl_tc5tab && ctx->tcd5.ok) {
-        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 7, kPoolSmem, nullptr, 0);
+    if (ctx->variant >= 7 && ctx->pl_tc && ctx->pl_tc5tab && ctx->tcd5.ok) {
+        // (ragged batches too, where tu_tc5.cu has the ragged form: its blocks permute while any sponge needs to)
+        const SpongeKernelEntry* k = find_kernel(ctx->field, (int)ctx->t, ctx->alpha, 7, kPoolSmem, nullptr, ragged);
         if (k && k->variant == 7) {
             r.k = k, r.pl = ctx->pl_tc, r.d = &ctx->tdesc;
             return r;

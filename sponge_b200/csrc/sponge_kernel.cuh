@@ -363,6 +363,33 @@ __global__ void PSD_LAUNCH_BOUNDS(T, VARIANT) sponge_kernel(const __grid_constan
                 k_out += emit_cnt;
                 rem_out -= emit_cnt;
             }
+#if PSD_POOL_KIND == 1
+            if constexpr (VARIANT == 7 && RAGGED) {
+                // Per-sponge lengths under a kernel whose permutation is a collective of the whole block (tile barriers,
+                // the block-wide switch of U): the block permutes as long as ANY of its sponges needs to.  A sponge that
+                // does not need this permutation runs it all the same and puts its state back afterwards.
+                const bool done = !perm && stage == 5;
+                if (__syncthreads_or(perm ? 1 : 0)) {
+                    uint32_t keep[T][8];
+                    if (!perm) {
+#pragma unroll
+                        for (int l = 0; l < T; l++)
+#pragma unroll
+                            for (int k = 0; k < 8; k++) keep[l][k] = st[l][k];
+                    }
+                    permute_tc5<F, T, ALPHA>(st, d, a.tc, tile);
+                    if (!perm) {
+#pragma unroll
+                        for (int l = 0; l < T; l++)
+#pragma unroll
+                            for (int k = 0; k < 8; k++) st[l][k] = keep[l][k];
+                    }
+                } else if (__syncthreads_and(done ? 1 : 0)) {
+                    break;
+                }
+                continue;
+            }
+#endif
             if (perm) {
 #if PSD_POOL_KIND == 1
                 if constexpr (VARIANT == 6) permute_tc<F, T, ALPHA>(st, d, a.tc, tcw);

@@ -23,6 +23,15 @@ typedef Bls12381Fr TuField;
         TuField::kFieldId, T, ALPHA, 7, 1, 0, PSD_MAX_BLOCK_T(T, 7), sponge_kernel<TuField, T, ALPHA, 7>, \
         "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=7,smem>"});
 
+// the same kernels with per-sponge absorb lengths (ragged batches): the block permutes while any of its sponges needs to
+#define PSD_REG_TC5_RAGGED(T, ALPHA)                                                                   \
+    static SpongeKernelRegistrar g_reg_tc5r_##T##_##ALPHA(SpongeKernelEntry{                            \
+        TuField::kFieldId, T, ALPHA, 7, 1, 1, PSD_MAX_BLOCK_T(T, 7), sponge_kernel<TuField, T, ALPHA, 7, 1, true>, \
+        "sponge_kernel<" PSD_TU_FNAME ",t=" #T ",alpha=" #ALPHA ",variant=7,smem,ragged>"});
+
+PSD_REG_TC5_RAGGED(3, 5)
+PSD_REG_TC5_RAGGED(3, 17)
+PSD_REG_TC5_RAGGED(5, 5)
 PSD_REG_TC5(3, 5)
 PSD_REG_TC5(3, 17)
 PSD_REG_TC5(2, 5)
