@@ -301,7 +301,7 @@ psd_status psd_imad_peak(psd_ctx* ctx, int kind, double* per_second, double* ela
  * 7 = the same contraction through tcgen05.mma.kind::i8 with the accumulators in tensor memory, and with
  *     every Montgomery reduction of the S-box done the same way (a reduction is a product by constants):
  *     the integer pipe only computes unreduced squares and products.  t = 2..5, alpha 5 or 17, both
- *     fields; the default.  Ragged batches at t = 3 and t = 5 too (the block permutes while any of its sponges
+ *     fields; the default.  Ragged batches too (the block permutes while any of its sponges
  *     needs to).  Where it has no kernel the request degrades to 6 (BN254)
  *     or to the integer variants (BLS12-381, where 6 measured slower than 3).
  * A request is served by the best kernel <= it that exists for the context's field, width and home of

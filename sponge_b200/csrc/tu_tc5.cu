@@ -32,6 +32,8 @@ typedef Bls12381Fr TuField;
 PSD_REG_TC5_RAGGED(3, 5)
 PSD_REG_TC5_RAGGED(3, 17)
 PSD_REG_TC5_RAGGED(5, 5)
+PSD_REG_TC5_RAGGED(2, 5)
+PSD_REG_TC5_RAGGED(4, 5)
 PSD_REG_TC5(3, 5)
 PSD_REG_TC5(3, 17)
 PSD_REG_TC5(2, 5)
